@@ -1,0 +1,331 @@
+// Host side of the feature cache: shard allocation, peer mapping, launches (stage 3).
+// Replaces the host classes of M/ssd_gnn_cache.cuh and the handle ctors of
+// M/isolated_cache.h:519-636 / M/nvshmem_cache.h:524-641.
+#include "cache.cuh"
+#include "distributor.h"
+#include <vector>
+
+namespace {
+
+thread_local std::string g_last_error;
+
+struct SlabHeader {  // first 256 bytes of every shard slab: lets a peer verify what it mapped
+    uint64_t magic, num_sets, row_bytes, num_colors;
+};
+constexpr uint64_t SLAB_MAGIC = 0xC0A1A6B200CAC4E0ULL;
+
+inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+struct SlabLayout {
+    size_t off_tags, off_seq, off_cmeta, off_ccnt, off_lines, total;
+    SlabLayout(uint64_t S, uint32_t R, int C) {
+        size_t o = 256;
+        off_tags = o;  o = align_up(o + S * COALA_WAYS * 8, 256);
+        off_seq = o;   o = align_up(o + S * 8, 256);
+        off_cmeta = o; o = align_up(o + S * COALA_WAYS * 4, 256);
+        off_ccnt = o;  o = align_up(o + (size_t)(C + 1) * 4, 4096);
+        off_lines = o; o = o + S * COALA_WAYS * (size_t)R;
+        total = o;
+    }
+    ShardView view(uint8_t* base) const {
+        ShardView v;
+        v.tags = reinterpret_cast<uint64_t*>(base + off_tags);
+        v.set_seq = reinterpret_cast<uint64_t*>(base + off_seq);
+        v.color_meta = reinterpret_cast<uint32_t*>(base + off_cmeta);
+        v.color_counters = reinterpret_cast<int32_t*>(base + off_ccnt);
+        v.lines = reinterpret_cast<uint4*>(base + off_lines);
+        return v;
+    }
+};
+
+}  // namespace
+
+void coala_set_error(const std::string& msg) { g_last_error = msg; }
+extern "C" const char* coala_last_error(void) { return g_last_error.c_str(); }
+extern "C" int coala_abi_version(void) { return 1; }
+
+struct coala_cache {
+    int kind, device, feat_dim, cache_dim, global_rank, local_rank, n_gpus, num_colors;
+    uint64_t num_sets;
+    uint32_t row_bytes;
+    uint8_t* slab = nullptr;
+    SlabLayout layout{1, 512, 0};
+    CacheParams params;
+    unsigned long long* d_stats = nullptr;
+    void* ipc_mapped[COALA_MAX_GPUS] = {nullptr};
+    int copy_engine = 0;
+    int sm_count = 148, blocks_per_sm = 4;
+    std::vector<int32_t> h_counters;
+};
+
+extern "C" int coala_cache_dim_for(int dim) {
+    if (dim <= 0) return -1;
+    if (dim <= 128) return 128;
+    if (dim <= 256) return 256;
+    if (dim <= 512) return 512;
+    if (dim <= 1024) return 1024;
+    return -1;  // "Only Feature Embedding Size less than 8KB is supported" (M/ssd_gnn_cache.cuh:43-44)
+}
+
+template <int VPL, bool SYS>
+static int launch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
+                         bool serial) {
+    if (n <= 0) return 0;
+    if (serial) {
+        coala_gather_kernel<VPL, SYS><<<1, 32, 0, st>>>(c->params, idx, out, n, n_dev);
+    } else {
+        const int threads = 256, wpb = threads / 32;
+        int64_t blocks = (n + wpb - 1) / wpb;
+        int64_t cap = (int64_t)c->sm_count * c->blocks_per_sm;
+        if (blocks > cap) blocks = cap;
+        coala_gather_kernel<VPL, SYS><<<(unsigned)blocks, threads, 0, st>>>(c->params, idx, out, n, n_dev);
+    }
+    COALA_CUDA(cudaGetLastError());
+    return 0;
+}
+
+static int dispatch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
+                           bool serial) {
+    const bool sys = c->kind == COALA_CACHE_PARTITIONED && c->n_gpus > 1;
+    const int vpl = c->row_bytes / 512;
+#define COALA_GO(V)                                                                        \
+    return sys ? launch_gather<V, true>(c, idx, out, n, n_dev, st, serial)                 \
+               : launch_gather<V, false>(c, idx, out, n, n_dev, st, serial)
+    switch (vpl) {
+        case 1: COALA_GO(1);
+        case 2: COALA_GO(2);
+        case 4: COALA_GO(4);
+        case 8: COALA_GO(8);
+    }
+#undef COALA_GO
+    COALA_FAIL("unsupported row size");
+}
+
+extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, coala_nd* nd, int global_rank, int local_rank,
+                                           int n_gpus, uint64_t cache_mb, uint64_t sim_buf_ptr) {
+    if (kind < 0 || kind > 2) { coala_set_error("coala_cache_create: bad kind"); return nullptr; }
+    int cache_dim = coala_cache_dim_for(feat_dim);
+    if (cache_dim < 0) { coala_set_error("Only Feature Embedding Size less than 8KB is supported"); return nullptr; }
+    if (sim_buf_ptr == 0) { coala_set_error("coala_cache_create: sim_buf_ptr == 0 (BaM/NVMe tier is out of scope; pass the pinned host feature table)"); return nullptr; }
+    if (n_gpus < 1 || n_gpus > COALA_MAX_GPUS) { coala_set_error("coala_cache_create: n_gpus out of range"); return nullptr; }
+    COALA_CUDA_NULL(cudaSetDevice(device));
+    coala_cache* c = new coala_cache();
+    c->kind = kind; c->device = device; c->feat_dim = feat_dim; c->cache_dim = cache_dim;
+    c->global_rank = global_rank; c->local_rank = local_rank; c->n_gpus = n_gpus;
+    c->row_bytes = (uint32_t)cache_dim * 4;                                  // page_size (M/ssd_gnn_cache.cuh:47)
+    uint64_t num_pages = cache_mb * 1024ULL * 1024ULL / c->row_bytes;        // (:96)
+    c->num_sets = num_pages / COALA_WAYS;                                    // (:97)
+    if (c->num_sets == 0) { coala_set_error("coala_cache_create: cache smaller than one set"); delete c; return nullptr; }
+    c->num_colors = nd ? coala_nd_num_colors(nd) : 0;
+    c->layout = SlabLayout(c->num_sets, c->row_bytes, c->num_colors);
+    cudaError_t e = cudaMalloc(&c->slab, c->layout.total);
+    if (e != cudaSuccess) { coala_set_error(std::string("cudaMalloc(cache slab) failed: ") + cudaGetErrorString(e)); delete c; return nullptr; }
+    ShardView own = c->layout.view(c->slab);
+    // tags: empty = id field all ones, version 0 (reference keys_ are memset 0xFF, M/isolated_cache.h:546)
+    {
+        std::vector<uint64_t> init(1 << 16, TAG_ID_MASK);
+        size_t ntags = c->num_sets * COALA_WAYS, done = 0;
+        // fill by doubling copies on the device
+        size_t first = std::min(ntags, init.size());
+        COALA_CUDA_NULL(cudaMemcpy(own.tags, init.data(), first * 8, cudaMemcpyHostToDevice));
+        done = first;
+        while (done < ntags) {
+            size_t chunk = std::min(done, ntags - done);
+            COALA_CUDA_NULL(cudaMemcpy(own.tags + done, own.tags, chunk * 8, cudaMemcpyDeviceToDevice));
+            done += chunk;
+        }
+    }
+    COALA_CUDA_NULL(cudaMemset(own.set_seq, 0, c->num_sets * 8));
+    COALA_CUDA_NULL(cudaMemset(own.color_meta, 0, c->num_sets * COALA_WAYS * 4));
+    COALA_CUDA_NULL(cudaMemset(own.color_counters, 0, (size_t)(c->num_colors + 1) * 4));
+    SlabHeader hdr{SLAB_MAGIC, c->num_sets, c->row_bytes, (uint64_t)c->num_colors};
+    COALA_CUDA_NULL(cudaMemcpy(c->slab, &hdr, sizeof(hdr), cudaMemcpyHostToDevice));
+    COALA_CUDA_NULL(cudaMalloc(&c->d_stats, 4 * sizeof(unsigned long long)));
+    COALA_CUDA_NULL(cudaMemset(c->d_stats, 0, 4 * sizeof(unsigned long long)));
+
+    CacheParams& p = c->params;
+    memset(&p, 0, sizeof(p));
+    p.my_slot = kind == COALA_CACHE_PARTITIONED ? local_rank : 0;
+    p.shard[p.my_slot] = own;
+    p.route_gpus = kind == COALA_CACHE_PARTITIONED ? n_gpus : 1;
+    p.hash_div = kind == COALA_CACHE_ISOLATED ? 1 : n_gpus;
+    p.row_bytes = c->row_bytes;
+    p.num_sets = c->num_sets;
+    p.host_feat = reinterpret_cast<const uint8_t*>(sim_buf_ptr);
+    p.color = nd ? coala_nd_color_dev_i32(nd) : nullptr;
+    p.track_color = (nd && p.color) ? 1 : 0;                                  // track_color = true (M/ssd_gnn_cache.cuh:67)
+    p.out_stride = feat_dim;
+    p.out_dim = feat_dim < cache_dim ? feat_dim : cache_dim;
+    p.stats = c->d_stats;
+
+    cudaDeviceProp prop;
+    COALA_CUDA_NULL(cudaGetDeviceProperties(&prop, device));
+    c->sm_count = prop.multiProcessorCount;
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, coala_gather_kernel<8, false>, 256, 0) == cudaSuccess && occ > 0)
+        c->blocks_per_sm = occ;
+    COALA_CUDA_NULL(cudaDeviceSynchronize());
+    return c;
+}
+
+extern "C" void coala_cache_destroy(coala_cache* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    cudaDeviceSynchronize();
+    for (int g = 0; g < COALA_MAX_GPUS; g++)
+        if (c->ipc_mapped[g]) cudaIpcCloseMemHandle(c->ipc_mapped[g]);
+    if (c->slab) cudaFree(c->slab);
+    if (c->d_stats) cudaFree(c->d_stats);
+    delete c;
+}
+
+extern "C" uint64_t coala_cache_num_sets(coala_cache* c) { return c->num_sets; }
+extern "C" int coala_cache_row_bytes(coala_cache* c) { return (int)c->row_bytes; }
+extern "C" uint64_t coala_cache_color_counters_dev_ptr(coala_cache* c) {
+    return (uint64_t)c->params.shard[c->params.my_slot].color_counters;
+}
+
+extern "C" int coala_cache_ipc_handle(coala_cache* c, void* handle64) {
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    COALA_CUDA(cudaSetDevice(c->device));
+    cudaIpcMemHandle_t h;
+    COALA_CUDA(cudaIpcGetMemHandle(&h, c->slab));
+    memcpy(handle64, &h, 64);
+    return 0;
+}
+
+static int attach_base(coala_cache* c, int peer, uint8_t* base) {
+    if (c->kind != COALA_CACHE_PARTITIONED) COALA_FAIL("attach: cache is not partitioned");
+    if (peer < 0 || peer >= c->n_gpus) COALA_FAIL("attach: peer rank out of range");
+    if (peer == c->params.my_slot) return 0;
+    SlabHeader hdr;
+    COALA_CUDA(cudaMemcpy(&hdr, base, sizeof(hdr), cudaMemcpyDefault));
+    if (hdr.magic != SLAB_MAGIC || hdr.num_sets != c->num_sets || hdr.row_bytes != c->row_bytes ||
+        hdr.num_colors != (uint64_t)c->num_colors)
+        COALA_FAIL("attach: peer shard geometry differs from ours");
+    c->params.shard[peer] = c->layout.view(base);
+    return 0;
+}
+
+extern "C" int coala_cache_attach_ipc(coala_cache* c, int peer, const void* handle64) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    if (peer == c->params.my_slot) return 0;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle64, 64);
+    void* base = nullptr;
+    COALA_CUDA(cudaIpcOpenMemHandle(&base, h, cudaIpcMemLazyEnablePeerAccess));
+    c->ipc_mapped[peer] = base;
+    return attach_base(c, peer, static_cast<uint8_t*>(base));
+}
+
+extern "C" int coala_cache_attach_local(coala_cache* c, int peer, coala_cache* other) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    if (other->device != c->device) {
+        int can = 0;
+        COALA_CUDA(cudaDeviceCanAccessPeer(&can, c->device, other->device));
+        if (!can) COALA_FAIL("attach_local: no P2P access between the two devices");
+        cudaError_t e = cudaDeviceEnablePeerAccess(other->device, 0);
+        if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) COALA_CUDA(e);
+        cudaGetLastError();
+    }
+    return attach_base(c, peer, other->slab);
+}
+
+static int check_ready(coala_cache* c) {
+    if (c->kind == COALA_CACHE_PARTITIONED)
+        for (int g = 0; g < c->n_gpus; g++)
+            if (!c->params.shard[g].tags) COALA_FAIL("partitioned cache: peer shard " + std::to_string(g) + " not attached");
+    return 0;
+}
+
+extern "C" int coala_cache_read_feature_async(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n,
+                                              uint64_t n_dev_ptr, void* stream) {
+    if (check_ready(c)) return -1;
+    COALA_CUDA(cudaSetDevice(c->device));
+    return dispatch_gather(c, reinterpret_cast<const int64_t*>(idx_ptr), reinterpret_cast<float*>(out_ptr), n,
+                           reinterpret_cast<const int64_t*>(n_dev_ptr), static_cast<cudaStream_t>(stream), false);
+}
+
+extern "C" int coala_cache_read_feature(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n) {
+    if (coala_cache_read_feature_async(c, out_ptr, idx_ptr, n, 0, nullptr)) return -1;
+    COALA_CUDA(cudaDeviceSynchronize());  // synchronous like the reference (M/ssd_gnn_cache.cuh:266)
+    return 0;
+}
+
+extern "C" int coala_cache_read_feature_serial(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n) {
+    if (check_ready(c)) return -1;
+    COALA_CUDA(cudaSetDevice(c->device));
+    if (dispatch_gather(c, reinterpret_cast<const int64_t*>(idx_ptr), reinterpret_cast<float*>(out_ptr), n, nullptr, nullptr, true))
+        return -1;
+    COALA_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+
+extern "C" int coala_cache_get_cache_data(coala_cache* c, uint64_t dst_ptr) {
+    // the reference copies num_color int32 out of zero-copy host memory (M/ssd_gnn_cache.cuh:176-186);
+    // here the counters live in HBM next to the shard and are fetched with one small copy.
+    COALA_CUDA(cudaSetDevice(c->device));
+    if (c->num_colors == 0) return 0;
+    COALA_CUDA(cudaMemcpy(reinterpret_cast<void*>(dst_ptr), c->params.shard[c->params.my_slot].color_counters,
+                          (size_t)c->num_colors * 4, cudaMemcpyDefault));
+    return 0;
+}
+
+extern "C" int coala_cache_get_cache_data_n(coala_cache* c, uint64_t dst_ptr, int count) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    if (count < 0 || count > c->num_colors + 1) COALA_FAIL("get_cache_data_n: count out of range");
+    if (count == 0) return 0;
+    COALA_CUDA(cudaMemcpy(reinterpret_cast<void*>(dst_ptr), c->params.shard[c->params.my_slot].color_counters,
+                          (size_t)count * 4, cudaMemcpyDefault));
+    return 0;
+}
+
+extern "C" int coala_cache_stats(coala_cache* c, uint64_t* hit, uint64_t* miss, uint64_t* bypass, int reset) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    unsigned long long h[4];
+    COALA_CUDA(cudaMemcpy(h, c->d_stats, sizeof(h), cudaMemcpyDeviceToHost));
+    if (hit) *hit = h[0];
+    if (miss) *miss = h[1];
+    if (bypass) *bypass = h[2];
+    if (reset) COALA_CUDA(cudaMemset(c->d_stats, 0, sizeof(h)));
+    return 0;
+}
+
+extern "C" int coala_cache_print_stats(coala_cache* c) {
+    uint64_t h, m, b;
+    if (coala_cache_stats(c, &h, &m, &b, 1)) return -1;
+    // same two lines as NVSHMEM_cache_d_t::print_stats (M/nvshmem_cache.h:133-142); bypasses are misses
+    printf("Global Rank: %i Local Rank:%i hit count: %llu miss count: %llu\n", c->global_rank, c->local_rank,
+           (unsigned long long)h, (unsigned long long)(m + b));
+    printf("Global Rank: %i Local Rank:%i  GPU hit ratio: %f\n", c->global_rank, c->local_rank,
+           (float)h / (float)(h + m + b));
+    fflush(stdout);
+    return 0;
+}
+
+extern "C" int coala_cache_export_state(coala_cache* c, uint64_t* keys, uint32_t* color_meta, uint32_t* set_cnt) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    COALA_CUDA(cudaDeviceSynchronize());
+    const ShardView& s = c->params.shard[c->params.my_slot];
+    size_t slots = c->num_sets * COALA_WAYS;
+    if (keys) {
+        COALA_CUDA(cudaMemcpy(keys, s.tags, slots * 8, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < slots; i++) {
+            uint64_t id = keys[i] & TAG_ID_MASK;
+            keys[i] = id == TAG_ID_MASK ? ~0ULL : id;  // reference encoding of an empty way
+        }
+    }
+    if (color_meta) COALA_CUDA(cudaMemcpy(color_meta, s.color_meta, slots * 4, cudaMemcpyDeviceToHost));
+    if (set_cnt) {
+        std::vector<uint64_t> seq(c->num_sets);
+        COALA_CUDA(cudaMemcpy(seq.data(), s.set_seq, c->num_sets * 8, cudaMemcpyDeviceToHost));
+        for (size_t i = 0; i < c->num_sets; i++) set_cnt[i] = (uint32_t)(seq[i] >> 1);
+    }
+    return 0;
+}
+
+extern "C" int coala_cache_set_copy_engine(coala_cache* c, int engine) {
+    if (engine != 0) COALA_FAIL("copy engine not available in this build");
+    c->copy_engine = engine;
+    return 0;
+}

@@ -1,0 +1,231 @@
+// Device-side layout and protocol of the feature cache (stage 3).
+//
+// What the reference does (M/isolated_cache.h:335-475, M/nvshmem_cache.h:336-480): one warp per
+// requested node id; set seqlock -> 32-way tag search -> way seqlock -> 4-byte/lane copy ->
+// re-check; on a miss round-robin evict, colour bookkeeping, fill the line from the pinned host
+// table, re-read the line, copy out.  Peer shards are served by their OWNER (request exchange,
+// owner-side kernels, NVSHMEM puts, 4 barriers per batch).
+//
+// What this build does instead (B200-first):
+//   * one fused kernel; the REQUESTER's warp resolves the id itself against whichever shard owns
+//     it — its own HBM or a peer's, mapped with CUDA IPC and read over NVLink/NVSwitch with plain
+//     loads — so there is no request exchange, no owner-side kernel and no barrier;
+//   * tag word = [version:24 | id:40]; an odd version marks a line being refilled.  The version
+//     is the line's seqlock (the reference's separate way-lock array is folded into the tag), so
+//     a hit costs: 256-B coalesced tag probe -> row -> 8-B re-check;
+//   * the per-set word is a real lock (CAS even->odd) whose value/2 is also the round-robin
+//     pointer (the reference bumps set_cnt_ exactly once per write section, so the two agree);
+//     writers re-probe under the lock, so two GPUs missing on the same id never duplicate a line;
+//   * rows move as 16-byte vectors held in registers: a miss forwards the host row to BOTH the
+//     line and the output from the same registers (the reference writes the line, re-reads it,
+//     then writes the output);
+//   * nobody waits unboundedly on another warp/GPU: a busy line or a contended set falls back to
+//     reading the (immutable) host row directly — counted as `bypass`.
+#pragma once
+#include "common.cuh"
+#include "../../include/coala_b200.h"
+
+constexpr uint64_t TAG_ID_MASK = (1ULL << 40) - 1;  // empty slot: id field all ones, version 0
+constexpr int TAG_VER_SHIFT = 40;
+
+struct ShardView {           // every pointer is valid in the address space of the process using it
+    uint64_t* tags;          // [S*32]  version<<40 | id
+    uint64_t* set_seq;       // [S]     odd = locked; value>>1 = number of fills = round-robin pointer
+    uint32_t* color_meta;    // [S*32]  colour of the resident line (M/isolated_cache.h color_meta_)
+    int32_t* color_counters; // [num_colors+1] lines per colour (M/isolated_cache.h color_counters)
+    uint4* lines;            // [S*32*R/16]
+};
+
+struct CacheParams {
+    ShardView shard[COALA_MAX_GPUS];
+    int route_gpus;          // id % route_gpus picks the shard (1 = always shard[my_slot])
+    int hash_div;            // set = (id / hash_div) % num_sets
+    int my_slot;             // index of this GPU's own shard in shard[]
+    uint32_t row_bytes;      // R = cache_dim * 4 (CL_SIZE)
+    uint64_t num_sets;
+    const uint8_t* host_feat;  // pinned host table, row stride R (reference sim_buf)
+    const int32_t* color;      // device copy of color[N] (reference reads the pinned int64 array)
+    int track_color;
+    int out_stride;          // floats between output rows (= feat_dim)
+    int out_dim;             // floats copied per output row (min(feat_dim, cache_dim))
+    unsigned long long* stats;  // [0]=hit [1]=miss [2]=bypass
+};
+
+constexpr int LOCK_TRIES = 64;     // CAS attempts on a set lock before bypassing
+constexpr int BUSY_POLLS = 256;    // polls of a line being filled by someone else before bypassing
+
+template <int VPL>
+__device__ __forceinline__ void store_out_row(const CacheParams& p, float* out_row, const uint4 (&v)[VPL], unsigned lane) {
+    if ((p.out_dim & 3) == 0 && (p.out_stride & 3) == 0) {
+        const int nvec = p.out_dim >> 2;
+#pragma unroll
+        for (int k = 0; k < VPL; k++) {
+            int vi = k * 32 + lane;
+            if (vi < nvec) st_out_v4(reinterpret_cast<uint4*>(out_row) + vi, v[k]);
+        }
+    } else {  // feat_dim not a multiple of 4 floats: rows are not 16-B aligned
+#pragma unroll
+        for (int k = 0; k < VPL; k++) {
+            int e = (k * 32 + lane) * 4;
+            const uint32_t w[4] = {v[k].x, v[k].y, v[k].z, v[k].w};
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (e + j < p.out_dim) out_row[e + j] = __uint_as_float(w[j]);
+        }
+    }
+}
+
+template <int VPL>
+__device__ __forceinline__ void load_host_row(const CacheParams& p, uint64_t id, uint4 (&v)[VPL], unsigned lane) {
+    const uint4* src = reinterpret_cast<const uint4*>(p.host_feat + id * (uint64_t)p.row_bytes);
+#pragma unroll
+    for (int k = 0; k < VPL; k++) v[k] = ld_host_v4(src + k * 32 + lane);
+}
+
+// Optimistic read of `slot` whose tag word was observed as `tw` (even version, id matches).
+// Returns true when the registers hold a consistent copy of the line.
+template <int VPL, bool SYS>
+__device__ __forceinline__ bool read_line_validated(const ShardView& sh, uint64_t slot, uint64_t tw, uint32_t row_vecs,
+                                                    uint4 (&v)[VPL], unsigned lane) {
+    const uint4* src = sh.lines + slot * row_vecs;
+#pragma unroll
+    for (int k = 0; k < VPL; k++) v[k] = ld_line_v4<SYS>(src + k * 32 + lane);
+    fence_acq_rel<SYS>();  // order the row loads before the re-check (seqlock reader)
+    uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + slot);
+    return t2 == tw;  // warp-uniform: every lane loads the same word
+}
+
+// One warp resolves one node id. Returns 0 hit, 1 miss (filled), 2 bypass.
+template <int VPL, bool SYS>
+__device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, float* out_row, unsigned lane) {
+    const int g = p.route_gpus > 1 ? (int)(id % (uint64_t)p.route_gpus) : p.my_slot;
+    const ShardView& sh = p.shard[g];
+    const uint64_t set = (id / (uint64_t)p.hash_div) % p.num_sets;
+    const uint64_t slot0 = set * COALA_WAYS;
+    const uint32_t row_vecs = p.row_bytes >> 4;
+    uint4 v[VPL];
+
+    // ---- fast path: probe 32 tags with one coalesced 256-B access
+    uint64_t t = ld_acquire_u64<SYS>(sh.tags + slot0 + lane);
+    unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
+    if (m) {
+        int way = __ffs(m) - 1;
+        uint64_t tw = __shfl_sync(0xffffffffu, t, way);
+        if (((tw >> TAG_VER_SHIFT) & 1) == 0 && read_line_validated<VPL, SYS>(sh, slot0 + way, tw, row_vecs, v, lane)) {
+            store_out_row<VPL>(p, out_row, v, lane);
+            return 0;
+        }
+    }
+
+    // ---- slow path. Start the host read now: it overlaps the lock round trips, and the host
+    // table is immutable so the registers are valid whatever happens to the line meanwhile.
+    load_host_row<VPL>(p, id, v, lane);
+
+    uint64_t s = 0;
+    bool locked = false;
+    if (lane == 0) {
+        unsigned ns = 32;
+        for (int tries = 0; tries < LOCK_TRIES; tries++) {
+            s = ld_relaxed_u64<SYS>(sh.set_seq + set);
+            if ((s & 1) == 0 && cas_acquire_u64<SYS>(sh.set_seq + set, s, s + 1) == s) { locked = true; break; }
+            __nanosleep(ns);
+            if (ns < 1024) ns <<= 1;
+        }
+    }
+    locked = __shfl_sync(0xffffffffu, (int)locked, 0);
+    s = __shfl_sync(0xffffffffu, s, 0);
+    if (!locked) {  // contended set: serve from host, do not cache
+        store_out_row<VPL>(p, out_row, v, lane);
+        return 2;
+    }
+
+    // ---- under the set lock: re-probe (someone may have filled it since the optimistic probe)
+    t = ld_acquire_u64<SYS>(sh.tags + slot0 + lane);
+    m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
+    if (m) {
+        // present (possibly still being filled by another warp / GPU): nothing to modify,
+        // so restore the even value — readers that sampled `s` stay valid, no way is consumed.
+        if (lane == 0) st_release_u64<SYS>(sh.set_seq + set, s);
+        int way = __ffs(m) - 1;
+        const uint64_t slot = slot0 + way;
+        uint64_t tw = __shfl_sync(0xffffffffu, t, way);
+        for (int poll = 0; poll < BUSY_POLLS; poll++) {
+            if ((tw & TAG_ID_MASK) != id) break;  // evicted again meanwhile
+            if (((tw >> TAG_VER_SHIFT) & 1) == 0) {
+                if (read_line_validated<VPL, SYS>(sh, slot, tw, row_vecs, v, lane)) {
+                    store_out_row<VPL>(p, out_row, v, lane);
+                    return 0;
+                }
+            } else {
+                __nanosleep(256);
+            }
+            tw = ld_acquire_u64<SYS>(sh.tags + slot);
+        }
+        load_host_row<VPL>(p, id, v, lane);  // registers were reused for the line: host copy is bit-identical
+        store_out_row<VPL>(p, out_row, v, lane);
+        return 2;
+    }
+
+    // ---- miss: round-robin victim (M/isolated_cache.h:198-212: way = set_cnt++ % num_ways)
+    const int way = (int)((s >> 1) & (COALA_WAYS - 1));
+    const uint64_t slot = slot0 + way;
+    const uint64_t told = __shfl_sync(0xffffffffu, t, way);
+    if ((told >> TAG_VER_SHIFT) & 1) {  // victim is still being filled by a writer 32 fills ago
+        if (lane == 0) st_release_u64<SYS>(sh.set_seq + set, s);
+        store_out_row<VPL>(p, out_row, v, lane);
+        return 2;
+    }
+    const uint64_t ver = (told >> TAG_VER_SHIFT) + 1;  // odd: line busy
+    if (lane == 0) {
+        st_relaxed_u64<SYS>(sh.tags + slot, (ver << TAG_VER_SHIFT) | id);
+        if (p.track_color) {  // M/isolated_cache.h:432-446
+            uint32_t oldc = sh.color_meta[slot];
+            uint32_t newc = (uint32_t)p.color[id];
+            sh.color_meta[slot] = newc;
+            red_add_s32<SYS>(sh.color_counters + oldc, -1);
+            red_add_s32<SYS>(sh.color_counters + newc, 1);
+        }
+        st_release_u64<SYS>(sh.set_seq + set, s + 2);  // unlock; the line stays busy via its tag
+        fence_acq_rel<SYS>();                            // busy tag visible before any line data
+    }
+    __syncwarp();
+
+    // ---- fill: host row -> line and -> output from the same registers
+    uint4* dst = sh.lines + slot * row_vecs;
+#pragma unroll
+    for (int k = 0; k < VPL; k++) st_line_v4<SYS>(dst + k * 32 + lane, v[k]);
+    store_out_row<VPL>(p, out_row, v, lane);
+    __syncwarp();
+    if (lane == 0) {
+        fence_acq_rel<SYS>();  // cumulative: the whole warp's line stores precede the publish
+        st_relaxed_u64<SYS>(sh.tags + slot, ((ver + 1) << TAG_VER_SHIFT) | id);
+    }
+    return 1;
+}
+
+template <int VPL, bool SYS>
+__global__ void __launch_bounds__(256) coala_gather_kernel(CacheParams p, const int64_t* __restrict__ idx,
+                                                           float* __restrict__ out, int64_t n,
+                                                           const int64_t* __restrict__ n_dev) {
+    __shared__ unsigned s_stat[3];
+    if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
+    __syncthreads();
+    if (n_dev) n = min(n, *n_dev);
+    const unsigned lane = lane_id();
+    const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+    unsigned n_hit = 0, n_miss = 0, n_byp = 0;
+    for (int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n; r += warps_total) {
+        const uint64_t id = (uint64_t)__ldg(idx + r);
+        int res = resolve_row<VPL, SYS>(p, id, out + r * (int64_t)p.out_stride, lane);
+        n_hit += res == 0;
+        n_miss += res == 1;
+        n_byp += res == 2;
+    }
+    if (lane == 0) {
+        if (n_hit) atomicAdd(&s_stat[0], n_hit);
+        if (n_miss) atomicAdd(&s_stat[1], n_miss);
+        if (n_byp) atomicAdd(&s_stat[2], n_byp);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
+}

@@ -1,0 +1,176 @@
+// Shared UVA host memory (stage-2/3 substrate), synthetic feature tables, link probes and the
+// partition / un-permute kernels of the NCCL all-to-all comparison backend.
+#include "common.cuh"
+#include "../../include/coala_b200.h"
+#include <cerrno>
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+// ------------------------------------------------------------------------------------------
+// SharedUVAManager (M/shared_UVA.cuh:26-115) without MPI: the caller orders create/open.
+// ------------------------------------------------------------------------------------------
+struct coala_uva {
+    std::string path;
+    void* host = nullptr;
+    void* dev = nullptr;
+    int64_t bytes = 0;
+    int fd = -1;
+    bool creator = false;
+    bool registered = false;
+};
+
+extern "C" coala_uva* coala_uva_create(const char* shm_path, int64_t bytes, int create, int device, int zero) {
+    if (bytes <= 0) { coala_set_error("coala_uva_create: size must be positive"); return nullptr; }
+    COALA_CUDA_NULL(cudaSetDevice(device));
+    coala_uva* h = new coala_uva();
+    h->path = shm_path; h->bytes = bytes; h->creator = create != 0;
+    h->fd = create ? shm_open(shm_path, O_CREAT | O_RDWR, S_IRUSR | S_IWUSR)     // (:67)
+                   : shm_open(shm_path, O_RDWR, S_IRUSR | S_IWUSR);               // (:80)
+    if (h->fd < 0) { coala_set_error(std::string("shm_open failed, Reason=") + strerror(errno)); delete h; return nullptr; }
+    if (create && ftruncate(h->fd, bytes) != 0) {
+        coala_set_error(std::string("ftruncate failed, Reason=") + strerror(errno));
+        close(h->fd); shm_unlink(shm_path); delete h; return nullptr;
+    }
+    h->host = mmap(nullptr, (size_t)bytes, PROT_READ | PROT_WRITE, MAP_SHARED, h->fd, 0);   // (:83)
+    if (h->host == MAP_FAILED) {
+        coala_set_error(std::string("mmap failed, Reason= ") + strerror(errno));
+        close(h->fd); if (create) shm_unlink(shm_path); delete h; return nullptr;
+    }
+    if (create && zero) memset(h->host, 0, (size_t)bytes);                                   // (:99)
+    cudaError_t e = cudaHostRegister(h->host, (size_t)bytes, cudaHostRegisterDefault);       // (:89)
+    if (e != cudaSuccess) {
+        coala_set_error(std::string("cudaHostRegister error: ") + cudaGetErrorString(e));
+        munmap(h->host, (size_t)bytes); close(h->fd); if (create) shm_unlink(shm_path); delete h; return nullptr;
+    }
+    h->registered = true;
+    e = cudaHostGetDevicePointer(&h->dev, h->host, 0);                                        // (:94)
+    if (e != cudaSuccess) {
+        coala_set_error(std::string("cudaHostGetDevicePointer error: ") + cudaGetErrorString(e));
+        coala_uva_cleanup(h, create); delete h; return nullptr;
+    }
+    return h;
+}
+extern "C" uint64_t coala_uva_host_ptr(coala_uva* h) { return (uint64_t)h->host; }
+extern "C" uint64_t coala_uva_device_ptr(coala_uva* h) { return (uint64_t)h->dev; }
+extern "C" int coala_uva_cleanup(coala_uva* h, int unlink_segment) {
+    if (h->host) {
+        if (h->registered) cudaHostUnregister(h->host);
+        munmap(h->host, (size_t)h->bytes);
+        h->host = nullptr; h->dev = nullptr; h->registered = false;
+    }
+    if (h->fd >= 0) { close(h->fd); h->fd = -1; }
+    if (unlink_segment) shm_unlink(h->path.c_str());
+    return 0;
+}
+extern "C" void coala_uva_destroy(coala_uva* h) {
+    if (!h) return;
+    coala_uva_cleanup(h, h->creator);
+    delete h;
+}
+
+// ------------------------------------------------------------------------------------------
+// synthetic feature table + verification (same integer hash as oracle/c/common.c)
+// ------------------------------------------------------------------------------------------
+__global__ void synth_fill_kernel(float* __restrict__ dst, uint64_t seed, int64_t row0, int64_t nrows, int dim, int64_t stride) {
+    // one warp per row, 4 floats per lane per step
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    for (int64_t r = warp; r < nrows; r += nwarps) {
+        const uint64_t hr = mix64(seed ^ (uint64_t)(row0 + r));
+        float* p = dst + r * stride;
+        if ((dim & 3) == 0 && (stride & 3) == 0) {
+            for (int c = lane * 4; c < dim; c += 128) {
+                float4 v = make_float4(feat_from_hash(mix64(hr + c)), feat_from_hash(mix64(hr + c + 1)),
+                                       feat_from_hash(mix64(hr + c + 2)), feat_from_hash(mix64(hr + c + 3)));
+                *reinterpret_cast<float4*>(p + c) = v;
+            }
+        } else {
+            for (int c = lane; c < dim; c += 32) p[c] = feat_from_hash(mix64(hr + c));
+        }
+    }
+}
+
+extern "C" int coala_synth_fill_features(uint64_t dst_ptr, uint64_t seed, int64_t row0, int64_t nrows, int dim,
+                                         int64_t stride_floats, void* stream) {
+    if (nrows <= 0) return 0;
+    int64_t blocks = (nrows + 7) / 8;
+    if (blocks > 148 * 16) blocks = 148 * 16;
+    synth_fill_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float*>(dst_ptr), seed, row0,
+                                                                                   nrows, dim, stride_floats);
+    COALA_CUDA(cudaGetLastError());
+    if (!stream) COALA_CUDA(cudaDeviceSynchronize());
+    return 0;
+}
+
+__global__ void synth_check_kernel(const float* __restrict__ rows, const int64_t* __restrict__ idx, int64_t n, int dim,
+                                   int64_t stride, uint64_t seed, unsigned long long* __restrict__ bad) {
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const uint64_t hr = mix64(seed ^ (uint64_t)idx[r]);
+        const float* p = rows + r * stride;
+        bool ok = true;
+        for (int c = lane; c < dim; c += 32)
+            ok &= __float_as_uint(p[c]) == __float_as_uint(feat_from_hash(mix64(hr + c)));
+        if (__ballot_sync(0xffffffffu, !ok) && lane == 0) atomicAdd(bad, 1ULL);
+    }
+}
+
+extern "C" int coala_synth_check_rows(uint64_t rows_ptr, uint64_t idx_ptr, int64_t n, int dim, int64_t stride_floats,
+                                      uint64_t seed, int64_t* mismatches) {
+    unsigned long long* d_bad;
+    COALA_CUDA(cudaMalloc(&d_bad, 8));
+    COALA_CUDA(cudaMemset(d_bad, 0, 8));
+    if (n > 0) {
+        int64_t blocks = (n + 7) / 8;
+        if (blocks > 148 * 16) blocks = 148 * 16;
+        synth_check_kernel<<<(unsigned)blocks, 256>>>(reinterpret_cast<const float*>(rows_ptr), reinterpret_cast<const int64_t*>(idx_ptr),
+                                                      n, dim, stride_floats, seed, d_bad);
+        COALA_CUDA(cudaGetLastError());
+    }
+    unsigned long long bad = 0;
+    COALA_CUDA(cudaMemcpy(&bad, d_bad, 8, cudaMemcpyDeviceToHost));
+    cudaFree(d_bad);
+    *mismatches = (int64_t)bad;
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
+// streaming-read probe: measures what a kernel can pull through a link (pinned host over PCIe,
+// a peer's HBM over NVLink, or local HBM) — the denominators of the per-link rooflines
+// ------------------------------------------------------------------------------------------
+__global__ void probe_read_kernel(const uint4* __restrict__ src, int64_t nvec, unsigned* __restrict__ sink) {
+    unsigned acc = 0;
+    const int64_t stride = (int64_t)gridDim.x * blockDim.x;
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < nvec; i += 4 * stride) {
+        uint4 a = ld_host_v4(src + i), b = ld_host_v4(src + i + stride), c = ld_host_v4(src + i + 2 * stride),
+              d = ld_host_v4(src + i + 3 * stride);
+        acc ^= a.x ^ b.y ^ c.z ^ d.w;
+    }
+    for (; i < nvec; i += stride) acc ^= ld_host_v4(src + i).x;
+    if (acc == 0x12345677u) *sink = acc;  // keep the loads alive
+}
+
+extern "C" int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int iters, double* gb_per_s) {
+    unsigned* sink;
+    COALA_CUDA(cudaMalloc(&sink, 4));
+    cudaEvent_t e0, e1;
+    COALA_CUDA(cudaEventCreate(&e0));
+    COALA_CUDA(cudaEventCreate(&e1));
+    const int64_t nvec = bytes / 16;
+    probe_read_kernel<<<148 * 8, 256>>>(reinterpret_cast<const uint4*>(src_ptr), nvec, sink);  // warm-up
+    COALA_CUDA(cudaEventRecord(e0));
+    for (int i = 0; i < iters; i++) probe_read_kernel<<<148 * 8, 256>>>(reinterpret_cast<const uint4*>(src_ptr), nvec, sink);
+    COALA_CUDA(cudaEventRecord(e1));
+    COALA_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    COALA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    *gb_per_s = (double)nvec * 16.0 * iters / (ms * 1e-3) / 1e9;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    return 0;
+}

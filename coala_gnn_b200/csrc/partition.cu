@@ -1,0 +1,112 @@
+// Kernels of the NCCL all-to-all comparison backend:
+//   split_node_list : nccl_split_node_list_kernel (M/cache_kernel.cu:79-91) buckets ids by
+//                     id % G with atomicAdd slots, so the order inside a bucket changes run to run.
+//                     Here it is a stable partition (count -> scan -> scatter): bucket g holds its
+//                     ids in request order, which also makes the owner-side cache state reproducible.
+//   map_feat_data   : nccl_gather_feature_kernel + block_memcpy<ulonglong4> (M/cache_kernel.cu:113-137):
+//                     out[map[r]] = src[r]; one warp per row, 16-byte vectors.
+#include "common.cuh"
+#include "../../include/coala_b200.h"
+
+namespace {
+constexpr int PT = 1024;  // ids per block
+
+__device__ __forceinline__ int stable_rank_in_block(int g, int G, int (*warp_cnt)[COALA_MAX_GPUS], int* my_warp_base) {
+    // rank of this thread among the block's threads with the same bucket; g < 0 = inactive
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int rank = 0;
+    for (int j = 0; j < G; j++) {
+        unsigned b = __ballot_sync(0xffffffffu, g == j);
+        if (g == j) rank = __popc(b & ((1u << lane) - 1));
+        if (lane == 0) warp_cnt[w][j] = __popc(b);
+    }
+    __syncthreads();
+    if (threadIdx.x < G) {
+        int acc = 0;
+        for (int ww = 0; ww < PT / 32; ww++) { int x = warp_cnt[ww][threadIdx.x]; warp_cnt[ww][threadIdx.x] = acc; acc += x; }
+        my_warp_base[threadIdx.x] = acc;  // block total for bucket threadIdx.x
+    }
+    __syncthreads();
+    return g >= 0 ? warp_cnt[w][g] + rank : 0;
+}
+
+__global__ void __launch_bounds__(PT) part_count_kernel(const int64_t* __restrict__ idx, int64_t n, int G, int* __restrict__ block_cnt) {
+    __shared__ int warp_cnt[PT / 32][COALA_MAX_GPUS];
+    __shared__ int tot[COALA_MAX_GPUS];
+    const int64_t i = (int64_t)blockIdx.x * PT + threadIdx.x;
+    const int g = i < n ? (int)((uint64_t)idx[i] % (uint64_t)G) : -1;
+    stable_rank_in_block(g, G, warp_cnt, tot);
+    if (threadIdx.x < G) block_cnt[(int64_t)blockIdx.x * G + threadIdx.x] = tot[threadIdx.x];
+}
+
+__global__ void part_scan_kernel(int* __restrict__ block_cnt, int nblocks, int G, int64_t* __restrict__ counter) {
+    const int g = threadIdx.x;
+    if (g >= G) return;
+    int acc = 0;
+    for (int b = 0; b < nblocks; b++) { int x = block_cnt[(int64_t)b * G + g]; block_cnt[(int64_t)b * G + g] = acc; acc += x; }
+    counter[g] = acc;
+}
+
+__global__ void __launch_bounds__(PT) part_scatter_kernel(const int64_t* __restrict__ idx, int64_t n, int G, int max_sample,
+                                                          const int* __restrict__ block_base, int64_t* __restrict__ node,
+                                                          int64_t* __restrict__ map) {
+    __shared__ int warp_cnt[PT / 32][COALA_MAX_GPUS];
+    __shared__ int tot[COALA_MAX_GPUS];
+    const int64_t i = (int64_t)blockIdx.x * PT + threadIdx.x;
+    int64_t id = 0;
+    int g = -1;
+    if (i < n) { id = idx[i]; g = (int)((uint64_t)id % (uint64_t)G); }
+    const int r = stable_rank_in_block(g, G, warp_cnt, tot);
+    if (g >= 0) {
+        const int64_t slot = (int64_t)max_sample * g + block_base[(int64_t)blockIdx.x * G + g] + r;
+        node[slot] = id;
+        map[slot] = i;
+    }
+}
+
+__global__ void unpermute_rows_kernel(float* __restrict__ out, const float* __restrict__ src, const int64_t* __restrict__ map,
+                                      int64_t n, int dim) {
+    const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    const int lane = threadIdx.x & 31;
+    for (int64_t r = warp; r < n; r += nwarps) {
+        const int64_t d = map[r];
+        if ((dim & 3) == 0) {
+            const uint4* s = reinterpret_cast<const uint4*>(src + r * dim);
+            uint4* o = reinterpret_cast<uint4*>(out + d * dim);
+            for (int v = lane; v < dim / 4; v += 32) st_out_v4(o + v, ld_host_v4(s + v));
+        } else {
+            for (int c = lane; c < dim; c += 32) out[d * dim + c] = src[r * dim + c];
+        }
+    }
+}
+}  // namespace
+
+extern "C" int coala_split_node_list(uint64_t idx_ptr, int64_t n, uint64_t node_ptr, uint64_t map_ptr, uint64_t counter_ptr,
+                                     int n_gpus, int max_sample, void* stream) {
+    if (n_gpus < 1 || n_gpus > COALA_MAX_GPUS) COALA_FAIL("split_node_list: n_gpus out of range");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int64_t* counter = reinterpret_cast<int64_t*>(counter_ptr);
+    if (n <= 0) { COALA_CUDA(cudaMemsetAsync(counter, 0, n_gpus * 8, st)); return 0; }
+    const int nblocks = (int)((n + PT - 1) / PT);
+    int* block_cnt = nullptr;
+    COALA_CUDA(cudaMallocAsync(&block_cnt, (size_t)nblocks * n_gpus * sizeof(int), st));
+    const int64_t* idx = reinterpret_cast<const int64_t*>(idx_ptr);
+    part_count_kernel<<<nblocks, PT, 0, st>>>(idx, n, n_gpus, block_cnt);
+    part_scan_kernel<<<1, 32, 0, st>>>(block_cnt, nblocks, n_gpus, counter);
+    part_scatter_kernel<<<nblocks, PT, 0, st>>>(idx, n, n_gpus, max_sample, block_cnt, reinterpret_cast<int64_t*>(node_ptr),
+                                                reinterpret_cast<int64_t*>(map_ptr));
+    COALA_CUDA(cudaGetLastError());
+    COALA_CUDA(cudaFreeAsync(block_cnt, st));
+    return 0;
+}
+
+extern "C" int coala_map_feat_data(uint64_t out_ptr, uint64_t src_ptr, uint64_t map_ptr, int64_t n, int feat_dim, void* stream) {
+    if (n <= 0) return 0;
+    int64_t blocks = (n + 7) / 8;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    unpermute_rows_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<float*>(out_ptr), reinterpret_cast<const float*>(src_ptr), reinterpret_cast<const int64_t*>(map_ptr), n, feat_dim);
+    COALA_CUDA(cudaGetLastError());
+    return 0;
+}

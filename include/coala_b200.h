@@ -1,0 +1,192 @@
+/* coala_b200.h — C ABI of libcoala_b200.so: the B200-native (sm_100a) mini-batch data path of
+ * COALA-GNN.  Every entry point takes plain pointers and sizes (no torch, no pybind types) and
+ * is what a binding for the reference's COALA_GNN_Pybind module would call; the reference
+ * interface each one replaces is cited as file:line under /root/reference/COALA_GNN_Modules/
+ * (M/) and /root/reference/COALA-GNN-Setup/COALA_GNN/ (S/).
+ *
+ * Conventions
+ *   - handles are opaque pointers; NULL / non-zero return = failure, message via
+ *     coala_last_error() (thread-local copy of the last failure in this thread).
+ *   - "ptr" arguments typed uint64_t are raw addresses exactly as the reference passes them
+ *     from tensor.data_ptr(); unless stated they may be host or device
+ *     addresses and are classified with cudaPointerGetAttributes.
+ *   - calls without a stream argument are synchronous like the reference's (every cache
+ *     method there ends in cudaDeviceSynchronize, M/ssd_gnn_cache.cuh:125,169,266);
+ *     *_async variants enqueue on the given cudaStream_t (passed as void*) and return.
+ */
+#ifndef COALA_B200_H
+#define COALA_B200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define COALA_MAX_GPUS 16
+#define COALA_WAYS 32
+
+const char* coala_last_error(void);
+int coala_abi_version(void);
+
+/* ------------------------------------------------------------------ shared UVA host memory
+ * replaces SharedUVAManager (M/shared_UVA.cuh:26-115; bound at M/COALA_GNN_Pybind.cu:28-32).
+ * create!=0: shm_open(O_CREAT)+ftruncate (the local-rank-0 branch, :65-77); create==0: open
+ * an existing segment (:78-81).  Both mmap + cudaHostRegister + cudaHostGetDevicePointer
+ * (:83-98).  The MPI barrier between the two branches is the caller's (torch.distributed).
+ * zero!=0 clears the segment like the reference's memset (:99). */
+typedef struct coala_uva coala_uva;
+coala_uva* coala_uva_create(const char* shm_path, int64_t bytes, int create, int device, int zero);
+uint64_t coala_uva_host_ptr(coala_uva* h);
+uint64_t coala_uva_device_ptr(coala_uva* h);
+int coala_uva_cleanup(coala_uva* h, int unlink_segment); /* M/shared_UVA.cuh:102-110 */
+void coala_uva_destroy(coala_uva* h);
+
+/* ------------------------------------------------------------------ stage 1: seed distributor
+ * replaces Node_distributor_pybind (M/node_distributor_pybind.cuh:112-238; bound at
+ * M/COALA_GNN_Pybind.cu:53-57). */
+typedef struct coala_nd coala_nd;
+/* ctor (:138-148): loads color.npy (int64[N]), topk.npy (int64[C,K]), score.npy (f8[C,K]) with
+ * the reference's header rules (:37-109), keeps a pinned host copy of the colour table and
+ * uploads int32 colour / topk / score tables to `device`.  item_ptr is the caller-owned int64
+ * seed list (host or device). */
+coala_nd* coala_nd_create(uint64_t item_ptr, int node_id, int batch_size, int local_size, int n_domains,
+                          const char* color_file, const char* topk_file, const char* score_file, int device);
+/* same, tables given in memory (host pointers) instead of .npy files */
+coala_nd* coala_nd_create_from_arrays(uint64_t item_ptr, int node_id, int batch_size, int local_size, int n_domains,
+                                      const int64_t* color, int64_t n_nodes, const int64_t* topk,
+                                      const double* score, int num_colors, int K, int device);
+/* ctor without colour information (:133-135) */
+coala_nd* coala_nd_create_plain(uint64_t item_ptr, int n_domains);
+/* distribute_node_with_affinity (:150-222): bit-exact bucket assignment on the GPU; writes this
+ * domain's batch*local_size seeds (arrival order) to out_ptr. meta_ptrs[n_meta] are the per-domain
+ * int32 cache colour histograms (length >= num_colors+1 entries are read up to the largest
+ * colour id referenced). */
+int coala_nd_distribute(coala_nd* h, uint64_t offset, uint64_t out_ptr, const uint64_t* meta_ptrs, int n_meta);
+int coala_nd_distribute_async(coala_nd* h, uint64_t offset, uint64_t out_dev_ptr, const uint64_t* meta_dev_ptrs,
+                              int n_meta, void* stream);
+/* how many int32 entries each cache-meta histogram holds (default num_colors, the size the
+ * reference's callers allocate, S/Training_node_distributor.py:33; colour id == num_colors then
+ * reads as 0 instead of one past the end). Set num_colors+1 to cover every colour id. */
+int coala_nd_set_meta_len(coala_nd* h, int len);
+/* bucket_len[n_domains] after the last synchronous distribute (test hook) */
+int coala_nd_last_bucket_len(coala_nd* h, int* out);
+int coala_nd_num_colors(coala_nd* h);            /* get_num_colors (:224-226) */
+uint64_t coala_nd_color_host_ptr(coala_nd* h);   /* get_color_buffer_ptr (:228-231) */
+int64_t coala_nd_num_graph_nodes(coala_nd* h);
+void coala_nd_destroy(coala_nd* h);
+
+/* ------------------------------------------------------------------ stage 3: feature cache
+ * replaces SSD_GNN_SSD_Controllers (M/ssd_gnn_cache.cuh:10-55), Isolated_Cache (:205-372),
+ * SSD_GNN_NVSHMEM_Cache (:58-200) and the kernels of M/cache_kernel.cu. */
+/* cache_dim rounding 128/256/512/1024 (M/ssd_gnn_cache.cuh:34-44); -1 when dim > 1024 */
+int coala_cache_dim_for(int feat_dim);
+
+typedef struct coala_cache coala_cache;
+enum { COALA_CACHE_ISOLATED = 0,    /* private cache, set = id % S            (M/isolated_cache.h:183-188) */
+       COALA_CACHE_PARTITIONED = 1, /* owner = id % G, set = (id/G) % S, peers reached by P2P loads
+                                       (replaces the NVSHMEM owner-push of M/nvshmem_cache.h:336-480) */
+       COALA_CACHE_NCCL_SHARD = 2   /* local shard of an id%G partition, set = (id/G) % S; ids arrive by
+                                       all-to-all (M/isolated_cache.h:190-195 with nccl_cache=true) */ };
+/* ctor (M/ssd_gnn_cache.cuh:84-109, 227-252): num_sets = cache_mb*2^20/page/32. The distributor
+ * supplies the colour table and num_colors (may be NULL: colour tracking off). sim_buf_ptr is the
+ * pinned-host feature table (device-visible address, row stride = cache_dim*4 bytes), the
+ * reference's `sim_buf`; 0 is rejected (the BaM/NVMe tier is out of scope). */
+coala_cache* coala_cache_create(int kind, int device, int feat_dim, coala_nd* nd, int global_rank, int local_rank,
+                                int n_gpus, uint64_t cache_mb, uint64_t sim_buf_ptr);
+void coala_cache_destroy(coala_cache* c);
+uint64_t coala_cache_num_sets(coala_cache* c);
+int coala_cache_row_bytes(coala_cache* c);
+
+/* peer mapping for COALA_CACHE_PARTITIONED. One allocation per shard => one 64-byte CUDA IPC
+ * handle; exchange them with any transport, then attach every peer's. */
+int coala_cache_ipc_handle(coala_cache* c, void* handle64);
+int coala_cache_attach_ipc(coala_cache* c, int peer_local_rank, const void* handle64);
+/* same-process attachment (several shards driven from one process, or emulated ranks on one GPU) */
+int coala_cache_attach_local(coala_cache* c, int peer_local_rank, coala_cache* peer);
+
+/* Isolated_Cache::read_feature / Isolated_read_feature_kernel (M/ssd_gnn_cache.cuh:255-268,
+ * M/cache_kernel.cu:59-77) and, in PARTITIONED mode, the fused replacement of
+ * send_requests + read_feature (M/ssd_gnn_cache.cuh:111-174, M/cache_kernel.cu:4-57):
+ * out[i, 0:cache_dim] = feature row of idx[i]; out row stride = feat_dim floats. */
+int coala_cache_read_feature(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n);
+/* n_dev_ptr (optional, device int64*): the row count is read on the device so the launch can be
+ * captured in a CUDA graph; n is then the upper bound used for sizing. */
+int coala_cache_read_feature_async(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n,
+                                   uint64_t n_dev_ptr, void* stream);
+/* same kernel, launched as ONE warp so requests resolve strictly in order (test hook: makes
+ * hit/miss counts, tags and colour counters comparable with the sequential oracle) */
+int coala_cache_read_feature_serial(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n);
+/* get_cache_data (M/ssd_gnn_cache.cuh:176-186, 270-280): copies num_colors int32 counters */
+int coala_cache_get_cache_data(coala_cache* c, uint64_t dst_int32_ptr);
+/* same with an explicit entry count (<= num_colors+1) */
+int coala_cache_get_cache_data_n(coala_cache* c, uint64_t dst_int32_ptr, int count);
+uint64_t coala_cache_color_counters_dev_ptr(coala_cache* c);
+/* print_stats (M/ssd_gnn_cache.cuh:188-190, M/nvshmem_cache.h:133-142): counters since last reset */
+int coala_cache_stats(coala_cache* c, uint64_t* hit, uint64_t* miss, uint64_t* bypass, int reset);
+int coala_cache_print_stats(coala_cache* c);
+/* test hook: dumps tags (id field, 0xFF.. = empty), colour meta and round-robin pointers */
+int coala_cache_export_state(coala_cache* c, uint64_t* keys, uint32_t* color_meta, uint32_t* set_cnt);
+/* choose the row-copy engine: 0 = 16-byte vector loads (default), 1 = TMA bulk copies */
+int coala_cache_set_copy_engine(coala_cache* c, int engine);
+
+/* NCCL all-to-all variant helpers (comparison backend).
+ * split_node_list (M/ssd_gnn_cache.cuh:283-295, M/cache_kernel.cu:79-91): deterministic stable
+ * partition by id % n_gpus: node[max_sample*g + k], map[...] = original position, counter[g]. */
+int coala_split_node_list(uint64_t idx_ptr, int64_t n, uint64_t node_ptr, uint64_t map_ptr, uint64_t counter_ptr,
+                          int n_gpus, int max_sample, void* stream);
+/* map_feat_data (M/ssd_gnn_cache.cuh:327-356, M/cache_kernel.cu:113-137): out[map[r]] = src[r] */
+int coala_map_feat_data(uint64_t out_ptr, uint64_t src_ptr, uint64_t map_ptr, int64_t n, int feat_dim, void* stream);
+
+/* ------------------------------------------------------------------ stage 2: UVA neighbour sampler
+ * replaces dgl MultiLayerNeighborSampler.sample on the UVA CSC graph (call site
+ * S/COALA_GNN_DataLoader.py:162; graph arrangement M/shared_UVA.cuh + examples/ssd_gnn_dataloader.py:496-524). */
+typedef struct coala_sampler coala_sampler;
+/* CSC arrays are device-visible addresses (pinned host through UVA, or HBM); edge_ids_ptr may be 0
+ * (edge id = CSC position). fanouts[L] in the reference's order (input layer first). */
+coala_sampler* coala_sampler_create(int device, uint64_t indptr_ptr, uint64_t indices_ptr, uint64_t edge_ids_ptr,
+                                    int64_t num_nodes, int max_seeds, const int* fanouts, int n_layers);
+void coala_sampler_destroy(coala_sampler* s);
+int64_t coala_sampler_max_sample(coala_sampler* s);
+/* enqueue all layers for `ns` seeds (device int64); results stay in the sampler's buffers */
+int coala_sampler_sample_async(coala_sampler* s, uint64_t seeds_dev_ptr, int ns, uint64_t rng_key, void* stream);
+/* after the stream is synchronised: counts[2*L+1] = n_src(l), n_edges(l) for l = 0..L-1 in
+ * reference block order (input layer first), then n_seeds */
+int coala_sampler_counts(coala_sampler* s, int64_t* counts);
+/* device addresses of layer l (reference block order): src node ids [n_src], edge_src_local [ne],
+ * edge_dst_local [ne], edge ids [ne]; dst nodes of layer l are the first n_dst src nodes */
+int coala_sampler_layer_ptrs(coala_sampler* s, int layer, uint64_t* src_nodes, uint64_t* edge_src, uint64_t* edge_dst,
+                             uint64_t* edge_id);
+uint64_t coala_sampler_input_count_dev_ptr(coala_sampler* s); /* device int64: n input nodes */
+
+/* ------------------------------------------------------------------ offline colour metadata
+ * replaces Graph_Coloring (M/graph_coloring.h:15-68, M/graph_coloring.cpp; bound at
+ * M/COALA_GNN_Pybind.cu:65-77). Host code, as in the reference. */
+typedef struct coala_gc coala_gc;
+coala_gc* coala_gc_create(uint64_t num_nodes);
+void coala_gc_destroy(coala_gc* g);
+void coala_gc_set_adj_csc(coala_gc* g, uint64_t indptr_ptr, uint64_t indices_ptr);
+void coala_gc_set_color_buffer(coala_gc* g, uint64_t ptr);
+void coala_gc_set_topk_color_buffer(coala_gc* g, uint64_t ptr);
+void coala_gc_set_topk_affinity_buffer(coala_gc* g, uint64_t ptr);
+void coala_gc_cpu_color_graph(coala_gc* g);
+void coala_gc_cpu_color_graph_optimized(coala_gc* g, uint64_t train_ptr, uint64_t n_train);
+void coala_gc_cpu_count_nearest_color(coala_gc* g);
+void coala_gc_cpu_count_nearest_color_less_memory(coala_gc* g);
+void coala_gc_cpu_calculate_color_affinity(coala_gc* g);
+uint64_t coala_gc_get_num_color(coala_gc* g);
+uint64_t coala_gc_get_num_color_node(coala_gc* g);
+
+/* ------------------------------------------------------------------ synthetic data + checks (GPU) */
+/* feat[r, c] = hash(seed, row0 + r, c) in [0,1), written through a device-visible address */
+int coala_synth_fill_features(uint64_t dst_ptr, uint64_t seed, int64_t row0, int64_t nrows, int dim, int64_t stride_floats,
+                              void* stream);
+/* counts rows of `rows`[n, stride] whose first `dim` floats differ bitwise from hash(seed, idx[i], c) */
+int coala_synth_check_rows(uint64_t rows_ptr, uint64_t idx_ptr, int64_t n, int dim, int64_t stride_floats, uint64_t seed,
+                           int64_t* mismatches);
+/* streaming-read bandwidth probe of a device-visible range (host link / peer link / HBM peaks) */
+int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int iters, double* gb_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COALA_B200_H */
