@@ -1,0 +1,172 @@
+"""Graph / sampler / block objects that stand in for the DGL pieces the reference's data path uses:
+``dgl.graph(('csc', (indptr, indices, edge_ids)))`` on UVA tensors (examples/ssd_gnn_dataloader.py:523),
+``dgl.dataloading.MultiLayerNeighborSampler(fanouts)`` (examples/sbatch_ssd_gnn_train.py:70-72) and its
+``sample(g, seeds) -> (input_nodes, output_nodes, blocks)`` (S/COALA_GNN_DataLoader.py:162).
+The sampling and to_block arithmetic runs in the CUDA kernels of csrc/sampler.cu."""
+import ctypes as C
+
+from ._lib import lib, check, check_handle
+from .pybind import tensor_from_ptr
+
+MASK = (1 << 64) - 1
+
+
+def _mix64(z):
+    z = (z + 0x9E3779B97F4A7C15) & MASK
+    z = ((z ^ (z >> 30)) * 0xBF58476D1CE4E5B9) & MASK
+    z = ((z ^ (z >> 27)) * 0x94D049BB133111EB) & MASK
+    return z ^ (z >> 31)
+
+
+def batch_key(seed, batch_idx, rank=0):
+    """RNG key of one mini-batch (oracle.batch_key is the same arithmetic)."""
+    return _mix64((seed & MASK) ^ _mix64((batch_idx * 0x100000001B3 + rank) & MASK))
+
+
+class UVAGraph:
+    """CSC graph whose arrays are device-visible tensors (pinned host through UVA, or HBM).
+    ``ndata`` holds per-node device tensors ('label', 'labels', masks) like the DGL graph."""
+
+    def __init__(self, indptr, indices, edge_ids=None, num_nodes=None, device=None):
+        self.indptr, self.indices, self.edge_ids = indptr, indices, edge_ids
+        self._num_nodes = int(num_nodes if num_nodes is not None else indptr.numel() - 1)
+        self.device = device if device is not None else indptr.device
+        self.ndata = {}
+
+    def number_of_nodes(self):
+        return self._num_nodes
+
+    num_nodes = number_of_nodes
+
+    def formats(self, *_):
+        return self
+
+
+class _Frame(dict):
+    """Per-block node data, gathered from the graph's ndata by node id on first access."""
+
+    def __init__(self, graph, nids):
+        super().__init__()
+        self._g, self._nids = graph, nids
+
+    def __missing__(self, key):
+        v = self._g.ndata[key][self._nids]
+        self[key] = v
+        return v
+
+    def keys(self):
+        return set(super().keys()) | set(self._g.ndata.keys())
+
+
+class Block:
+    """One bipartite layer: edges (edge_src[e] -> edge_dst[e]) in local ids; dst nodes are the first
+    ``num_dst_nodes`` src nodes. srcdata['_ID'] / dstdata['_ID'] are the global node ids (dgl.NID)."""
+
+    def __init__(self, graph, src_nodes, n_dst, edge_src, edge_dst, edge_id):
+        self.src_nodes, self.dst_nodes = src_nodes, src_nodes[:n_dst]
+        self.edge_src, self.edge_dst, self.edge_id = edge_src, edge_dst, edge_id
+        self.srcdata = _Frame(graph, self.src_nodes)
+        self.dstdata = _Frame(graph, self.dst_nodes)
+        self.srcdata["_ID"] = self.src_nodes
+        self.dstdata["_ID"] = self.dst_nodes
+        self.edata = {"_ID": edge_id}
+
+    def number_of_src_nodes(self):
+        return int(self.src_nodes.numel())
+
+    def number_of_dst_nodes(self):
+        return int(self.dst_nodes.numel())
+
+    num_src_nodes, num_dst_nodes = number_of_src_nodes, number_of_dst_nodes
+
+    def num_edges(self):
+        return int(self.edge_src.numel())
+
+    def edges(self):
+        return self.edge_src, self.edge_dst
+
+    def int(self):  # the training loop calls block.int().to(device) (examples/sbatch_ssd_gnn_train.py:139)
+        return self
+
+    def to(self, device):
+        return self
+
+
+class MultiLayerNeighborSampler:
+    """Uniform in-neighbour sampling without replacement, one round per fan-out in reverse order,
+    each followed by to_block. `seed` fixes the RNG stream; the k-th call uses batch_key(seed, k, rank)."""
+
+    def __init__(self, fanouts, seed=0, rank=0):
+        self.fanouts = [int(f) for f in fanouts]
+        self.seed, self.rank, self.calls = int(seed), int(rank), 0
+        self._h, self._graph_id, self._max_seeds = None, None, 0
+
+    def _ensure(self, g, n_seeds):
+        import torch
+        key = (g.indptr.data_ptr(), g.indices.data_ptr())
+        if self._h is not None and self._graph_id == key and n_seeds <= self._max_seeds:
+            return
+        if self._h is not None:
+            lib().coala_sampler_destroy(self._h)
+        dev = torch.device(g.device)
+        dev_index = dev.index if dev.index is not None else torch.cuda.current_device()
+        fan = (C.c_int * len(self.fanouts))(*self.fanouts)
+        eptr = g.edge_ids.data_ptr() if g.edge_ids is not None else 0
+        self._h = check_handle(lib().coala_sampler_create(dev_index, g.indptr.data_ptr(), g.indices.data_ptr(), eptr,
+                                                          g.number_of_nodes(), int(n_seeds), fan, len(self.fanouts)), "sampler")
+        self._graph_id, self._max_seeds = key, int(n_seeds)
+        self._device = "cuda:%d" % dev_index
+
+    def max_sample(self):
+        return int(lib().coala_sampler_max_sample(self._h))
+
+    def sample_async(self, g, seeds, rng_key=None, stream=0):
+        """Enqueue the whole multi-layer sample; results stay in the sampler's device buffers."""
+        self._ensure(g, seeds.numel())
+        if rng_key is None:
+            rng_key = batch_key(self.seed, self.calls, self.rank)
+        self.calls += 1
+        check(lib().coala_sampler_sample_async(self._h, seeds.data_ptr(), seeds.numel(), rng_key, stream), "sample")
+        self._last_g = g
+
+    def input_nodes_dev_ptrs(self):
+        """(device pointer of the input-node id buffer, device pointer of its int64 count)."""
+        src = C.c_uint64()
+        check(lib().coala_sampler_layer_ptrs(self._h, 0, C.byref(src), None, None, None))
+        return src.value, int(lib().coala_sampler_input_count_dev_ptr(self._h))
+
+    def collect(self, copy=True):
+        """Wait for the last sample_async and wrap the buffers. copy=False returns views that the next
+        sample overwrites."""
+        import torch
+        L = len(self.fanouts)
+        counts = (C.c_int64 * (2 * L + 1))()
+        check(lib().coala_sampler_counts(self._h, counts), "sampler counts")
+        g = self._last_g
+        blocks = []
+        for k in range(L):
+            n_src, ne = counts[2 * k], counts[2 * k + 1]
+            n_dst = counts[2 * (k + 1)] if k + 1 < L else counts[2 * L]
+            p = [C.c_uint64() for _ in range(4)]
+            check(lib().coala_sampler_layer_ptrs(self._h, k, *[C.byref(x) for x in p]))
+            ts = []
+            for ptr, n in zip(p, (n_src, ne, ne, ne)):
+                t = tensor_from_ptr(ptr.value, (n,), torch.int64, self._device, owner=self) if n > 0 else \
+                    torch.empty(0, dtype=torch.int64, device=self._device)
+                ts.append(t.clone() if copy else t)
+            blocks.append(Block(g, ts[0], n_dst, ts[1], ts[2], ts[3]))
+        return blocks[0].src_nodes, blocks[-1].dst_nodes, blocks
+
+    def sample(self, g, seeds, rng_key=None):
+        import torch
+        seeds = seeds.to(g.device) if str(seeds.device) != str(g.device) else seeds
+        self.sample_async(g, seeds.contiguous(), rng_key, torch.cuda.current_stream().cuda_stream)
+        return self.collect()
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().coala_sampler_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass

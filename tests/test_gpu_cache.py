@@ -1,0 +1,187 @@
+"""GPU parity tests of the feature-cache gather (stage 3), through the C ABI (COALA_GNN_Pybind
+mirror classes) against the sequential oracle. Bar: features bit-exact always; hit/miss counts,
+tags, colour metadata and colour counters exact when requests resolve in order (serial launch)."""
+import numpy as np
+import pytest
+
+import oracle
+from coala_gnn_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(n_nodes, dim, num_colors=40, seed=17):
+    import torch
+    from coala_gnn_b200.pybind import Node_distributor_pybind, SSD_GNN_SSD_Controllers
+    from coala_gnn_b200._lib import lib
+    cd = lib().coala_cache_dim_for(dim)
+    feat = oracle.fill_features(n_nodes, dim, seed, stride=cd)  # host rows have stride cache_dim (M/isolated_cache.h:328)
+    host = torch.from_numpy(feat).pin_memory()
+    color, topk, score = synth.random_color_meta(n_nodes, num_colors, 10, seed=1)
+    items = np.arange(64, dtype=np.int64)
+    nd = Node_distributor_pybind.from_arrays(items.ctypes.data, 0, 8, 1, 1, color, topk, score, device=0)
+    ctrl = SSD_GNN_SSD_Controllers(1, cd * 4, 1024, 0, 0, dim, True)
+    return dict(feat=feat, host=host, color=color, nd=nd, ctrl=ctrl, items=items, cd=cd, dim=dim, C=num_colors)
+
+
+def _read(cache, idx, dim, serial=False):
+    import torch
+    t = torch.from_numpy(np.ascontiguousarray(idx, dtype=np.int64)).cuda()
+    out = torch.full((len(idx), dim), -1.0, dtype=torch.float32, device="cuda")
+    if serial:
+        cache.read_feature_serial(out.data_ptr(), t.data_ptr(), len(idx))
+    else:
+        cache.read_feature(out.data_ptr(), t.data_ptr(), len(idx))
+    return out.cpu().numpy()
+
+
+def _check_state_equal(cache, model, gpu=0, C=40):
+    keys, cmeta, scnt = cache.export_state()
+    assert np.array_equal(keys, model.keys(gpu))
+    assert np.array_equal(cmeta.astype(np.uint64), model.color_meta(gpu))
+    assert np.array_equal(scnt, model.set_cnt(gpu))
+    cnt = np.zeros(C + 1, dtype=np.int32)
+    cache.get_cache_data(cnt.ctypes.data, C + 1)
+    assert np.array_equal(cnt, model.color_counters(gpu))
+
+
+@pytest.mark.parametrize("dim", [128, 256, 512, 1024])
+def test_isolated_serial_matches_oracle_exactly(dim):
+    from coala_gnn_b200.pybind import Isolated_Cache
+    s = _setup(6000, dim)
+    cache = Isolated_Cache(s["ctrl"], s["nd"], 0, 1, 1, s["host"].data_ptr())
+    model = oracle.CacheModel(1, s["cd"] * 4, color=s["color"], num_colors=s["C"])
+    assert cache.num_sets() == model.num_sets
+    rng = np.random.default_rng(dim)
+    for it in range(4):
+        idx = rng.integers(0, 6000, 1500)  # duplicates inside a batch included
+        got = _read(cache, idx, dim, serial=True)
+        exp = model.read(idx, s["feat"], dim)
+        assert np.array_equal(got.view(np.uint32), exp.view(np.uint32))
+    h, m, b = cache.stats()
+    assert (h, m) == model.stats() and b == 0
+    _check_state_equal(cache, model, C=s["C"])
+
+
+@pytest.mark.parametrize("dim", [128, 1024, 100, 101])
+def test_isolated_parallel_features_bit_exact_and_invariants(dim):
+    from coala_gnn_b200.pybind import Isolated_Cache
+    s = _setup(8000, dim)
+    cache = Isolated_Cache(s["ctrl"], s["nd"], 0, 1, 2, s["host"].data_ptr())
+    rng = np.random.default_rng(3)
+    total = 0
+    for it in range(6):
+        idx = rng.permutation(8000)[:5000] if it % 2 == 0 else rng.integers(0, 8000, 5000)
+        got = _read(cache, idx, dim)
+        assert np.array_equal(got.view(np.uint32), s["feat"][idx][:, :dim].view(np.uint32))
+        total += len(idx)
+    h, m, b = cache.stats()
+    assert h + m + b == total and h > 0 and m > 0
+    keys, cmeta, scnt = cache.export_state()
+    res = keys != np.uint64(0xFFFFFFFFFFFFFFFF)
+    ids = keys[res].astype(np.int64)
+    assert len(np.unique(ids)) == len(ids)  # writers re-probe under the set lock: never a duplicate line
+    assert np.array_equal(cmeta[res], s["color"][ids].astype(np.uint32))
+    cnt = np.zeros(s["C"] + 1, dtype=np.int32)
+    cache.get_cache_data(cnt.ctypes.data, s["C"] + 1)
+    hist = np.bincount(cmeta[res].astype(np.int64), minlength=s["C"] + 1)
+    assert np.array_equal(cnt[1:], hist[1:]) and cnt[0] == hist[0] - res.sum()
+    assert scnt.sum() == m
+
+
+def test_conflict_storm_single_set_and_empty_batch():
+    """Every id maps to the same set (eviction storm) while readers hit it; plus n = 0."""
+    from coala_gnn_b200.pybind import Isolated_Cache
+    s = _setup(64 * 300, 256)
+    cache = Isolated_Cache(s["ctrl"], s["nd"], 0, 1, 1, s["host"].data_ptr())
+    S = cache.num_sets()
+    assert _read(cache, np.zeros(0, dtype=np.int64), 256).shape == (0, 256)
+    rng = np.random.default_rng(5)
+    for it in range(5):
+        idx = (rng.integers(0, 150, 4000) * S + 3).astype(np.int64)  # all in set 3
+        got = _read(cache, idx, 256)
+        assert np.array_equal(got.view(np.uint32), s["feat"][idx].view(np.uint32))
+    h, m, b = cache.stats()
+    assert h + m + b == 5 * 4000
+
+
+def test_warm_cache_all_hits_and_get_cache_data_default_len():
+    from coala_gnn_b200.pybind import Isolated_Cache
+    s = _setup(3000, 128)
+    cache = Isolated_Cache(s["ctrl"], s["nd"], 0, 1, 4, s["host"].data_ptr())  # 8192 lines > 3000 nodes
+    idx = np.random.default_rng(0).permutation(3000)
+    _read(cache, idx, 128)
+    cache.stats(reset=True)
+    got = _read(cache, idx[::-1].copy(), 128)
+    assert np.array_equal(got.view(np.uint32), s["feat"][idx[::-1]].view(np.uint32))
+    assert cache.stats() == (3000, 0, 0)
+    cnt = np.full(s["C"], 12345, dtype=np.int32)
+    cache.get_cache_data(cnt.ctypes.data)  # reference signature: num_colors entries
+    hist = np.bincount(s["color"][idx], minlength=s["C"] + 1)
+    assert np.array_equal(cnt[1:], hist[1:s["C"]]) and cnt[0] == hist[0] - 3000
+
+
+@pytest.mark.parametrize("G", [2, 4])
+def test_partitioned_emulated_ranks_match_oracle(G):
+    """G shards on one GPU, one cache object per emulated rank, peers attached in-process; ranks
+    issue their batches one after the other (serial launches) so the whole domain is comparable
+    with the oracle's partitioned model: owner = id % G, set = (id/G) % S."""
+    from coala_gnn_b200.pybind import SSD_GNN_NVSHMEM_Cache, NVSHMEM_Manager
+    s = _setup(9000, 128)
+    caches = []
+    for g in range(G):
+        NVSHMEM_Manager.current_rank = g
+        caches.append(SSD_GNN_NVSHMEM_Cache(s["ctrl"], s["nd"], g, G, 1, s["host"].data_ptr()))
+    NVSHMEM_Manager.current_rank = None
+    for g in range(G):
+        for r in range(G):
+            if r != g:
+                caches[g].attach_local(r, caches[r])
+    model = oracle.CacheModel(1, 512, n_gpus=G, mode="partitioned", color=s["color"], num_colors=s["C"])
+    rng = np.random.default_rng(G)
+    for it in range(3):
+        for g in range(G):
+            idx = rng.permutation(9000)[:2000]
+            got = _read(caches[g], idx, 128, serial=True)
+            exp = model.read(idx, s["feat"], 128)
+            assert np.array_equal(got.view(np.uint32), exp.view(np.uint32))
+    for g in range(G):
+        _check_state_equal(caches[g], model, gpu=g, C=s["C"])
+    hm = np.array([c.stats() for c in caches]).sum(axis=0)
+    assert (hm[0], hm[1]) == model.stats() and hm[2] == 0
+    # parallel launches through the reference-shaped call pair
+    import torch
+    for g in range(G):
+        idx = rng.permutation(9000)[:4000]
+        t = torch.from_numpy(idx).cuda()
+        out = torch.zeros((4000, 128), device="cuda")
+        caches[g].send_requests(t.data_ptr(), 4000, 0, 4000)
+        caches[g].read_feature(out.data_ptr(), 0, 4000)
+        assert np.array_equal(out.cpu().numpy().view(np.uint32), s["feat"][idx].view(np.uint32))
+
+
+def test_nccl_helpers_partition_and_unpermute():
+    """split_node_list is a stable partition by id % G; map_feat_data inverts it."""
+    import torch
+    from coala_gnn_b200._lib import lib, check
+    G, n, max_sample, dim = 4, 5000, 6000, 128
+    rng = np.random.default_rng(1)
+    idx = rng.integers(0, 10 ** 6, n).astype(np.int64)
+    t = torch.from_numpy(idx).cuda()
+    node = torch.zeros(G * max_sample, dtype=torch.int64, device="cuda")
+    mp = torch.zeros(G * max_sample, dtype=torch.int64, device="cuda")
+    cnt = torch.zeros(G, dtype=torch.int64, device="cuda")
+    check(lib().coala_split_node_list(t.data_ptr(), n, node.data_ptr(), mp.data_ptr(), cnt.data_ptr(), G, max_sample, None))
+    torch.cuda.synchronize()
+    cnt_h = cnt.cpu().numpy()
+    rows = torch.zeros((n, dim), device="cuda")
+    src_all = torch.arange(n * dim, dtype=torch.float32, device="cuda").reshape(n, dim)
+    for g in range(G):
+        exp_pos = np.nonzero(idx % G == g)[0]
+        assert cnt_h[g] == len(exp_pos)
+        assert np.array_equal(node[g * max_sample: g * max_sample + cnt_h[g]].cpu().numpy(), idx[exp_pos])
+        assert np.array_equal(mp[g * max_sample: g * max_sample + cnt_h[g]].cpu().numpy(), exp_pos)
+        packed = src_all[torch.from_numpy(exp_pos).cuda()].contiguous()
+        check(lib().coala_map_feat_data(rows.data_ptr(), packed.data_ptr(), mp.data_ptr() + 8 * g * max_sample, int(cnt_h[g]), dim, None))
+    torch.cuda.synchronize()
+    assert torch.equal(rows, src_all)

@@ -1,0 +1,158 @@
+"""CPU tests: the oracle against the reference's golden vectors / compiled reference, and the
+host-side product code (npy loader rules, colouring, C-ABI exports). No GPU compute."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+import oracle
+from coala_gnn_b200 import synth
+from conftest import GOLDEN, ROOT
+
+
+def _golden(name):
+    return np.load(os.path.join(GOLDEN, name + ".npz"))
+
+
+# ---------------------------------------------------------------- distributor
+def test_distributor_oracle_matches_reference_golden():
+    g = _golden("distributor_2k")
+    col = _golden("coloring_2k")
+    items = g["items"]
+    for k in range(int(g["n_cases"])):
+        D, L, B, off = (int(x) for x in g["c%d_DLB" % k])
+        metas = list(g["c%d_meta" % k])
+        for node_id in range(D):
+            out, bl = oracle.distribute(items, off, node_id, B, L, D, col["color"], col["topk"], col["score"], metas)
+            assert np.array_equal(out, g["c%d_out" % k][node_id]), (k, node_id)
+            assert list(bl) == [B * L] * D
+
+
+@pytest.mark.skipif(not oracle.have_ref(), reason="oracle/_ref not built")
+def test_distributor_oracle_matches_compiled_reference(tmp_path):
+    col = _golden("coloring_20k")
+    cf, tf, sf = (str(tmp_path / x) for x in ("color.npy", "topk.npy", "score.npy"))
+    np.save(cf, col["color"]), np.save(tf, col["topk"]), np.save(sf, col["score"])
+    items = synth.train_ids(20000, seed=9)
+    for D, L, B in [(8, 1, 128), (2, 4, 128), (5, 3, 17)]:
+        metas = synth.random_cache_meta(col["topk"].shape[0], D, seed=D)
+        for node_id in range(D):
+            ref, _ = oracle.ref_distribute(items, 77, node_id, B, L, D, cf, tf, sf, metas)
+            out, _ = oracle.distribute(items, 77, node_id, B, L, D, col["color"], col["topk"], col["score"], metas)
+            assert np.array_equal(ref, out)
+
+
+def test_distributor_partition_property():
+    """Union over domains of the outputs is exactly the input slice (size-independent property)."""
+    n, C, K, D, L, B = 50000, 300, 10, 8, 1, 256
+    color, topk, score = synth.random_color_meta(n, C, K, seed=3)
+    items = synth.train_ids(n, seed=4)
+    metas = synth.random_cache_meta(C, D)
+    outs = [oracle.distribute(items, 0, j, B, L, D, color, topk, score, metas)[0] for j in range(D)]
+    assert np.array_equal(np.sort(np.concatenate(outs)), np.sort(items[:D * L * B]))
+
+
+# ---------------------------------------------------------------- colouring (product host code vs reference golden)
+@pytest.mark.parametrize("name", ["coloring_2k", "coloring_20k"])
+def test_coloring_product_matches_reference_golden(name):
+    from coala_gnn_b200.pybind import Graph_Coloring
+    g = _golden(name)
+    n, e, seed = int(g["n"]), int(g["e"]), int(g["seed"])
+    indptr, indices, _ = synth.make_csc(n, e, seed)
+    train = np.arange(int(n * 0.6), dtype=np.int64)
+    ctypes.CDLL("libc.so.6").srand(1)  # the reference never seeds rand()
+    gc = Graph_Coloring(n)
+    gc.set_adj_csc(indptr.ctypes.data, indices.ctypes.data)
+    color = np.zeros(n, dtype=np.int64)
+    gc.set_color_buffer(color.ctypes.data)
+    gc.cpu_color_graph_optimized(train.ctypes.data, len(train))
+    nc = gc.get_num_color()
+    assert nc == g["topk"].shape[0]
+    tk, sc = np.zeros(nc * 10, dtype=np.int64), np.zeros(nc * 10, dtype=np.float64)
+    gc.set_topk_color_buffer(tk.ctypes.data)
+    gc.set_topk_affinity_buffer(sc.ctypes.data)
+    gc.cpu_calculate_color_affinity()
+    assert np.array_equal(color, g["color"])
+    assert np.array_equal(tk.reshape(nc, 10), g["topk"])
+    assert np.array_equal(sc.view(np.uint64).reshape(nc, 10), g["score"].view(np.uint64))  # bit-exact doubles
+    assert not tk.reshape(nc, 10)[-1].any()  # last colour's row is never filled (reference quirk)
+
+
+# ---------------------------------------------------------------- cache model
+@pytest.mark.parametrize("mode,G", [("isolated", 1), ("partitioned", 4)])
+def test_cache_model_invariants(mode, G):
+    n, dim = 5000, 128
+    feat = oracle.fill_features(n, dim, 17)
+    color, topk, _ = synth.random_color_meta(n, 40, 10, seed=1)
+    cm = oracle.CacheModel(1, dim * 4, n_gpus=G, mode=mode, color=color, num_colors=40)
+    rng = np.random.default_rng(0)
+    total = 0
+    for _ in range(5):
+        idx = rng.integers(0, n, 3000)
+        out = cm.read(idx, feat)
+        assert np.array_equal(out.view(np.uint32), feat[idx].view(np.uint32))
+        total += len(idx)
+    h, m = cm.stats()
+    assert h + m == total
+    for g in range(G if mode == "partitioned" else 1):
+        keys, cmeta, cnt = cm.keys(g), cm.color_meta(g), cm.color_counters(g)
+        resident = keys != np.uint64(0xFFFFFFFFFFFFFFFF)
+        ids = keys[resident].astype(np.int64)
+        assert np.array_equal(cmeta[resident], color[ids].astype(np.uint64))
+        hist = np.bincount(cmeta[resident].astype(np.int64), minlength=41)
+        assert np.array_equal(cnt[1:], hist[1:])
+        assert cnt[0] == hist[0] - resident.sum()  # every first fill decrements colour 0
+        if mode == "partitioned":
+            assert np.all(ids % G == g)
+
+
+def test_feature_generator_is_exact_and_layout_free():
+    a = oracle.fill_features(10, 128, 5)
+    b = oracle.fill_features(4, 128, 5, row0=3, stride=1024)
+    assert np.array_equal(a[3:7], b[:, :128])
+    assert a.min() >= 0.0 and a.max() < 1.0
+
+
+# ---------------------------------------------------------------- C ABI
+def _declared_symbols():
+    txt = open(os.path.join(ROOT, "include", "coala_b200.h")).read()
+    txt = re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+    return sorted(set(re.findall(r"\b(coala_[a-z0-9_]+)\s*\(", txt)))
+
+
+def test_library_exports_every_declared_symbol():
+    from coala_gnn_b200 import _lib
+    L = _lib.lib()
+    names = _declared_symbols()
+    assert len(names) > 50
+    for name in names:
+        assert hasattr(L, name), name
+        assert name in _lib.SIGNATURES, "binding table lacks " + name
+    assert L.coala_abi_version() == 1
+
+
+def test_cache_dim_rounding_matches_reference():
+    from coala_gnn_b200._lib import lib
+    f = lib().coala_cache_dim_for  # M/ssd_gnn_cache.cuh:34-44
+    assert [f(d) for d in (1, 100, 128, 129, 256, 300, 512, 513, 1024)] == [128, 128, 128, 256, 256, 512, 512, 1024, 1024]
+    assert f(1025) == -1
+
+
+def test_npy_loader_error_behaviour(tmp_path):
+    """Same failure classes as parse_numpy_file (M/node_distributor_pybind.cuh:11-109), raised before any CUDA call."""
+    from coala_gnn_b200.pybind import Node_distributor_pybind
+    items = np.arange(100, dtype=np.int64)
+    good = str(tmp_path / "c.npy")
+    np.save(good, np.zeros(10, dtype=np.int64))
+    with pytest.raises(RuntimeError, match="Unable to open file"):
+        Node_distributor_pybind(items.ctypes.data, 0, 4, 1, 1, str(tmp_path / "missing.npy"), good, good, device=0)
+    bad = str(tmp_path / "bad.npy")
+    open(bad, "wb").write(b"not an npy file at all")
+    with pytest.raises(RuntimeError, match="Not a valid .npy file"):
+        Node_distributor_pybind(items.ctypes.data, 0, 4, 1, 1, bad, good, good, device=0)
+    f4 = str(tmp_path / "f4.npy")
+    np.save(f4, np.zeros(10, dtype=np.float32))
+    with pytest.raises(RuntimeError, match="dtype"):
+        Node_distributor_pybind(items.ctypes.data, 0, 4, 1, 1, f4, good, good, device=0)
