@@ -1,0 +1,346 @@
+#!/usr/bin/env python
+"""bench.py — mini-batches/s of the COALA-GNN data path (seed distribution -> UVA neighbour sampling
+-> cached feature gather) on synthetic IGB-shaped data.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+One JSON line on rank 0.  A "step" is one mini-batch (batch 1024, SAGE fan-out 5,5) per GPU.
+  value : device-resident pipeline (coala_gnn_b200.pipeline.DevicePipeline), CUDA-event timed;
+  e2e   : the drop-in COALA_GNN_DataLoader iterator with host seed lists / host metadata;
+  roofline : the gather kernel, timed live with CUDA events inside the timed region;
+  cpu_baseline : oracle sampler (OpenMP) + index_select on the host cores (bounded sample).
+`--impl reference` times that CPU path as its own arm.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+METRIC = "mini-batches/s (IGB-medium-shaped synthetic graph, SAGE fan-out 5,5, batch 1024 per GPU; seed distribution + UVA sampling + cached feature gather)"
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--warmup", type=int, default=20)
+    p.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    p.add_argument("--shape", default=os.environ.get("COALA_BENCH_SHAPE", "igb-medium"))
+    p.add_argument("--cache_size", type=int, default=16384, help="MB per GPU (reference flag name)")
+    p.add_argument("--cache_backend", default="nvshmem", choices=["nvshmem", "p2p", "isolated", "nccl"])
+    p.add_argument("--distribution", default="node_color", choices=["node_color", "baseline"])
+    p.add_argument("--batch_size", type=int, default=1024)
+    p.add_argument("--fan_out", default="5,5")
+    p.add_argument("--refresh_counter", type=int, default=10)
+    p.add_argument("--prewarm", type=int, default=-1, help="untimed batches that warm the cache (-1: one pass budgeted by --prewarm_seconds)")
+    p.add_argument("--prewarm_seconds", type=float, default=25.0)
+    p.add_argument("--cpu_baseline_seconds", type=float, default=12.0)
+    p.add_argument("--no_cpu_baseline", action="store_true")
+    return p.parse_args()
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index=0):
+        self.rows, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm)}
+
+
+def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads=None):
+    """The reference's CPU formulation of the path (BASELINE.json: "DGL CPU sampler + torch index_select
+    gather"): oracle OpenMP sampler + to_block, then a row gather from the host feature table."""
+    import oracle
+    indptr, indices, feat = ds_host
+    threads = threads or os.cpu_count()
+    max_sample = B
+    for f in fan:
+        max_sample *= f + 1
+    times, rows = [], 0
+    i = 0
+    t_end = time.time() + seconds if seconds else None
+    while True:
+        seeds = train[(i % (len(train) // B - 1)) * B:][:B]
+        t0 = time.perf_counter()
+        inp, _ = oracle.sample_blocks_fast(indptr, indices, seeds, fan, oracle.batch_key(1, i), max_sample, threads)
+        out = oracle.index_select(feat, inp, threads)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+            rows += len(inp)
+        i += 1
+        if steps is not None and len(times) >= steps:
+            break
+        if t_end is not None and time.time() > t_end and len(times) >= 3:
+            break
+    del out
+    tot = float(np.sum(times))
+    return {"batches_per_s": len(times) / tot, "ms_per_step": 1e3 * tot / len(times), "rows_per_step": rows / len(times),
+            "gather_GBs": rows * feat.shape[1] * 4 / tot / 1e9, "steps": len(times), "threads": threads}
+
+
+def build_world(args):
+    import torch
+    from COALA_GNN import MPI_Comm_Manager, Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
+    from coala_gnn_b200.datasets import SyntheticSharedCSCUVA
+    from coala_gnn_b200 import synth
+    comm = MPI_Comm_Manager(-1)  # one cache domain spanning all ranks of the box
+    torch.cuda.set_device(comm.device_index)
+    device = "cuda:%d" % comm.device_index
+    ds = SyntheticSharedCSCUVA(args.shape, comm, device, verbose=True)
+    fan = [int(f) for f in args.fan_out.split(",")]
+    train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=0))
+    nd = Node_Distributor(comm, train, args.batch_size, ds.color_file, ds.topk_file, ds.score_file, parsing_method=args.distribution)
+    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank)
+    backend = args.cache_backend
+    loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, sampler, args.batch_size, ds.dim, fan,
+                                  args.cache_size, device, refresh_counter=args.refresh_counter, cache_backend=backend,
+                                  sim_buf=ds.feat_data)
+    return comm, ds, train, fan, nd, sampler, loader, device
+
+
+def barrier_sync(comm):
+    import torch
+    import torch.distributed as dist
+    torch.cuda.synchronize()
+    if comm.global_size > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def max_over_ranks(comm, x, device):
+    import torch
+    import torch.distributed as dist
+    if comm.global_size == 1:
+        return x
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return float(t.item())
+
+
+def sum_over_ranks(comm, xs, device):
+    import torch
+    import torch.distributed as dist
+    if comm.global_size == 1:
+        return list(xs)
+    t = torch.tensor(list(xs), dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+    return [float(v) for v in t.tolist()]
+
+
+def run_ours(args):
+    import ctypes as C
+    import torch
+    from coala_gnn_b200._lib import lib, check
+    from coala_gnn_b200.pipeline import DevicePipeline
+    comm, ds, train, fan, nd, sampler, loader, device = build_world(args)
+    N, B, R = comm.global_size, args.batch_size, ds.cache_dim * 4
+    cache = loader.COALA_GNN_Manager.COALA_GNN_Cache
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    if os.path.exists(peaks_path):
+        hbm_peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json"
+    gb = C.c_double()
+    check(lib().coala_probe_read_bandwidth(ds.feat_data.data_ptr(), min(ds.num_nodes * R, 4 << 30), 2, C.byref(gb)))
+    host_peak = gb.value
+
+    pipe = DevicePipeline(loader, record_gather_events=True)
+    spe = pipe.steps_per_epoch()
+
+    def pipe_steps(n):
+        for _ in range(n):
+            if pipe.step_idx % spe == spe - 1:
+                pipe.reset()
+            pipe.step()
+
+    # ---- untimed cache pre-warm through the real path (steady state is what an epoch sees)
+    t0 = time.time()
+    n_pre = 0
+    budget = args.prewarm if args.prewarm >= 0 else 10 ** 9
+    while n_pre < budget:
+        pipe_steps(50)
+        torch.cuda.synchronize()
+        n_pre += 50
+        if args.prewarm < 0 and time.time() - t0 > args.prewarm_seconds:
+            break
+    pre_stats = cache.stats(reset=True)
+    pipe.events.clear()
+
+    # ---- value: device-resident pipeline
+    pipe_steps(args.warmup)
+    barrier_sync(comm)
+    cache.stats(reset=True)
+    pipe.events.clear()
+    clocks = ClockSampler(comm.device_index) if comm.global_rank == 0 else None
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    pipe_steps(args.steps)
+    e1.record()
+    barrier_sync(comm)
+    dev_ms = max_over_ranks(comm, e0.elapsed_time(e1), device)
+    clk = clocks.stop() if clocks else None
+    h, m, b = cache.stats(reset=True)
+    gather_ms = float(np.mean(pipe.gather_ms()))
+    rows = (h + m + b) / args.steps
+    value = N * args.steps / (dev_ms * 1e-3)
+
+    # ---- e2e: the drop-in iterator (host seed list, host colour metadata, per-step D2H of the result ids)
+    it = iter(loader)
+    loader.scheduler.refresh_counter = args.refresh_counter
+    pin = torch.empty(B, dtype=torch.int64).pin_memory()
+
+    def loader_steps(n):
+        nonlocal it
+        last = None
+        for _ in range(n):
+            try:
+                last = next(it)
+            except StopIteration:
+                it = iter(loader)
+                last = next(it)
+            pin.copy_(last[1], non_blocking=True)  # D2H read of the step's result header (seeds)
+        return last
+
+    loader_steps(max(3, args.warmup // 2))
+    barrier_sync(comm)
+    cache.stats(reset=True)
+    t0 = time.perf_counter()
+    loader_steps(args.steps)
+    torch.cuda.synchronize()
+    e2e_s = max_over_ranks(comm, time.perf_counter() - t0, device)
+    barrier_sync(comm)
+    eh, em, eb = cache.stats(reset=True)
+    e2e_value = N * args.steps / e2e_s
+    L = comm.local_size
+    h2d = B * 8 + (B * L * 8 if comm.is_master else 0) + (nd.meta_len * 4 * comm.num_master_process) / 1.0  # seeds + seed slice staging + metadata
+    d2h = B * 8 + (B * L * 8 if comm.is_master else 0) + 8 * (2 * len(fan) + 1) + nd.meta_len * 4 / args.refresh_counter
+
+    hs, ms_, bs = sum_over_ranks(comm, [h, m, b], device)
+    out = None
+    if comm.global_rank == 0:
+        miss_rows = (m + b) / args.steps
+        alg_hbm = 2.0 * R * rows  # 2R per gathered row (line->out on a hit, line+out written on a miss)
+        alg_host = R * miss_rows
+        t_hbm, t_host = alg_hbm / (hbm_peak * 1e9), alg_host / (host_peak * 1e9)
+        t_meas = gather_ms * 1e-3
+        binding = "host_link" if t_host > t_hbm else "hbm"
+        out = {
+            "metric": METRIC, "value": value, "unit": "mini-batches/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "data": "synthetic", "impl": "ours",
+            "config": {"workload": "%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), SAGE fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
+                       % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, B, args.cache_size, args.cache_backend, comm.num_master_process, L, args.distribution),
+                       "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (> 126 MB L2, no reuse between steps)" % (rows * R / 1e6),
+                       "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter},
+            "hit_ratio": hs / max(1.0, hs + ms_ + bs), "rows_per_step": rows,
+            "gather_GBs": rows * R / t_meas / 1e9,
+            "roofline": {"bound": "hbm", "achieved": alg_hbm / t_meas / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": alg_hbm / t_meas / 1e9 / hbm_peak,
+                         "traffic": None, "peak_source": peak_src, "kernel": "coala_gather_kernel", "kernel_ms": gather_ms,
+                         "kernel_share_of_step": gather_ms / (dev_ms / args.steps),
+                         "binding_link": binding, "binding_frac": max(t_hbm, t_host) / t_meas,
+                         "host_link": {"achieved": alg_host / t_meas / 1e9, "peak": host_peak, "unit": "GB/s", "frac": alg_host / t_meas / 1e9 / host_peak,
+                                       "peak_source": "coala_probe_read_bandwidth (UVA streaming read, this run)"}},
+            "e2e": {"value": e2e_value, "unit": "mini-batches/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "host_link_feature_bytes_per_step": int(R * (em + eb) / args.steps), "hit_ratio": eh / max(1, eh + em + eb),
+                    "api": "COALA_GNN_DataLoader.__next__"},
+            "gpu_launches": pipe.kernels_per_step * args.steps,
+            "clocks": clk,
+        }
+    return comm, ds, train, fan, out
+
+
+def main():
+    args = parse_args()
+    world = int(os.environ.get("WORLD_SIZE", 1))
+    rank = int(os.environ.get("RANK", 0))
+    if args.impl == "reference":
+        if rank != 0:
+            return 0
+        os.environ["WORLD_SIZE"], os.environ["RANK"] = "1", "0"
+        from COALA_GNN import MPI_Comm_Manager
+        from coala_gnn_b200.datasets import SyntheticSharedCSCUVA
+        from coala_gnn_b200 import synth
+        comm = MPI_Comm_Manager(0)
+        ds = SyntheticSharedCSCUVA(args.shape, comm, "cuda:0", verbose=True)
+        try:
+            fan = [int(f) for f in args.fan_out.split(",")]
+            train = synth.train_ids(ds.num_nodes, seed=0)
+            r = cpu_path((ds.csc_host[0], ds.csc_host[1], ds.feat_host_array()), train, args.batch_size, fan, steps=args.steps, warmup=args.warmup)
+            line = {"metric": METRIC, "value": r["batches_per_s"], "unit": "mini-batches/s", "n_gpus": args.gpus, "steps": args.steps,
+                    "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+                    "dtype": "f32", "data": "synthetic", "impl": "reference",
+                    "config": {"workload": "%s, SAGE fan-out %s, batch %d: CPU sampler (OpenMP restatement of the DGL CPU sampler, DGL absent) + index_select gather on %d host threads"
+                               % (args.shape, args.fan_out, args.batch_size, r["threads"])},
+                    "cpu_baseline": {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
+                                     "sample": "%d mini-batches of %d seeds (%.0f gathered rows each)" % (r["steps"], args.batch_size, r["rows_per_step"])},
+                    "gather_GBs": r["gather_GBs"],
+                    "e2e": {"value": r["batches_per_s"], "unit": "mini-batches/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+            print(json.dumps(line), flush=True)
+        finally:
+            ds.cleanup()
+        return 0
+
+    if args.gpus > 1 and world == 1:  # convenience: plain `python bench.py --gpus N` re-launches itself under torchrun
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
+               "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
+        return subprocess.call(cmd)
+    comm = ds = None
+    try:
+        comm, ds, train, fan, out = run_ours(args)
+        if comm.global_rank == 0:
+            if world == 1 and not args.no_cpu_baseline:
+                r = cpu_path((ds.csc_host[0], ds.csc_host[1], ds.feat_host_array()), train.numpy(), args.batch_size, fan,
+                             seconds=args.cpu_baseline_seconds)
+                out["cpu_baseline"] = {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
+                                       "sample": "%d mini-batches of %d seeds in %.1f s (oracle OpenMP sampler + index_select, %.1f GB/s gathered)"
+                                                 % (r["steps"], args.batch_size, r["steps"] / r["batches_per_s"], r["gather_GBs"])}
+            print(json.dumps(out), flush=True)
+    finally:
+        if comm is not None and comm.global_size > 1:
+            import torch.distributed as dist
+            try:
+                dist.barrier()
+            except Exception:
+                pass
+        if ds is not None:
+            ds.cleanup()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -139,12 +139,12 @@ class Shared_UVA_Tensor_Manager(object):
     """S/Shared_Tensor.py:118-179: one POSIX shm segment per tensor, created by local rank 0,
     mapped + pinned by every rank of the machine, exposed as a torch "cuda" tensor (UVA alias)."""
 
-    def __init__(self, comm_manager, path, tensor_size):
+    def __init__(self, comm_manager, path, tensor_size, zero=True):
         self.comm_manager = comm_manager
         self.tensor_size = int(tensor_size)
         self.device = "cuda:" + str(comm_manager.device_index)
         self.memory_handle = SharedUVAManager(path, self.tensor_size, comm_manager.node_id, 0, comm_manager.local_comm,
-                                              device=comm_manager.device_index)
+                                              device=comm_manager.device_index, zero=zero)
         self.device_ptr = self.memory_handle.get_device_ptr()
         self.host_ptr = self.memory_handle.get_host_ptr()
 

@@ -1,0 +1,141 @@
+"""Mirror of S/COALA_GNN_DataLoader.py: the iterator that glues seed distribution -> neighbour
+sampling -> cached feature gather, yielding (input_nodes, output_nodes, blocks, feat)."""
+import threading
+
+import torch
+
+from .manager import COALA_GNN_Manager
+
+
+class COALA_GNN_Node_Distribution_Scheduler(object):
+    """S/COALA_GNN_DataLoader.py:8-75. Distribution of batch t+1 runs on a thread during batch t
+    (the C ABI call releases the GIL); cache colour metadata is refreshed every `refresh_counter`
+    batches into a double buffer."""
+
+    def __init__(self, node_distributor, ssd_gnn_manager, refresh_counter=8):
+        self.node_distributor = node_distributor
+        self.ssd_gnn_manager = ssd_gnn_manager
+        self.metadata_reuse_counter = 0
+        self.refresh_counter = refresh_counter
+        self.cache_color_gathered_header = 0
+        self.distribute_thread = None
+        self.cache_meta_gather_thread = None
+        self.cache_meta_tensor = torch.zeros(self.node_distributor.meta_len, dtype=torch.int32)
+
+    def run(self, is_last: bool):
+        nd = self.node_distributor
+        comm = nd.comm_manager
+        if comm.is_master:
+            if self.distribute_thread is None:  # first stage of the pipeline (:31-35)
+                self.distribute_thread = threading.Thread(target=nd.parse_domain_training_nodes, args=(self.cache_color_gathered_header,))
+                self.distribute_thread.start()
+            self.distribute_thread.join()
+            self.distribute_thread = None
+
+        distributed_node_index = nd.parsed_training_nodes_buffer[nd.parsed_training_nodes_buffer_header]
+        comm.broadcast_training_nodes(distributed_node_index)
+        nd.parsed_training_nodes_buffer_header = (nd.parsed_training_nodes_buffer_header + 1) % 2
+
+        if self.metadata_reuse_counter == self.refresh_counter:  # (:46-59)
+            self.metadata_reuse_counter = 0
+            if self.cache_meta_gather_thread is not None:
+                self.cache_meta_gather_thread.join()
+                nd.cache_color_db_header = int((nd.cache_color_db_header + 1) % 2)
+            self.ssd_gnn_manager.COALA_GNN_Cache.get_cache_data(self.cache_meta_tensor.data_ptr(), nd.meta_len)
+            self.cache_color_gathered_header = int((nd.cache_color_db_header + 1) % 2)
+            self.cache_meta_gather_thread = threading.Thread(target=nd.gather_cache_meta, args=(self.cache_meta_tensor,))
+            self.cache_meta_gather_thread.start()
+
+        if comm.is_master and not is_last:  # (:64-68)
+            self.distribute_thread = threading.Thread(target=nd.parse_domain_training_nodes, args=(self.cache_color_gathered_header,))
+            self.distribute_thread.start()
+
+        self.metadata_reuse_counter += 1
+        lr = comm.local_rank
+        return distributed_node_index[(lr * nd.batch_size):((lr + 1) * nd.batch_size)]  # (:71-75)
+
+    def drain(self):
+        for t in (self.distribute_thread, self.cache_meta_gather_thread):
+            if t is not None:
+                t.join()
+        self.distribute_thread = None
+        self.cache_meta_gather_thread = None
+
+
+class SSD_INFO(object):
+    def __init__(self, num_ssds, page_size, num_elems, ssd_read_offset):
+        self.num_ssds = num_ssds
+        self.num_elems = num_elems
+        self.ssd_read_offset = ssd_read_offset
+        self.page_size = page_size
+
+
+class COALA_GNN_DataLoader(object):
+    """S/COALA_GNN_DataLoader.py:92-174 — same constructor arguments and iterator contract."""
+
+    def __init__(self, SSD_info, node_distributor, graph, graph_sampler, batch_size, dim, fan_out, cache_size, device,
+                 refresh_counter=10, cache_backend="nvshmem", sim_buf=None, shuffle=False):
+        self.refresh_counter = refresh_counter
+        self.sampler = graph_sampler
+        self.batch_size = batch_size
+        self.g = graph
+        self.SSD_info = SSD_info
+        self.cache_backend = cache_backend
+        self.node_distributor = node_distributor
+        self.device = device
+        self.COALA_GNN_Manager = COALA_GNN_Manager(
+            node_distributor=node_distributor, page_size=SSD_info.page_size, num_ssds=SSD_info.num_ssds,
+            num_elems=SSD_info.num_elems, ssd_read_offset=SSD_info.ssd_read_offset, cache_size=cache_size,
+            batch_size=batch_size, fan_out=fan_out, dim=dim, MPI_comm_manager=node_distributor.comm_manager,
+            device=device, cache_backend=cache_backend, sim_buf=sim_buf)
+        self.scheduler = COALA_GNN_Node_Distribution_Scheduler(node_distributor=self.node_distributor,
+                                                               ssd_gnn_manager=self.COALA_GNN_Manager,
+                                                               refresh_counter=self.refresh_counter)
+        self.counter = 0
+        self.index_len = len(self.node_distributor.index_tensor)
+        self.total_count = int(self.index_len / self.node_distributor.global_batch_size) - 1  # (:139-141)
+        # fused path: sampler output feeds the gather on the device without a host round trip
+        self.fused = cache_backend in ("nvshmem", "p2p", "isolated") and hasattr(self.sampler, "sample_async")
+        self._seed_buf = torch.empty(batch_size, dtype=torch.int64, device=device)
+        self._seed_pin = torch.empty(batch_size, dtype=torch.int64).pin_memory() if torch.cuda.is_available() else None
+
+    def __iter__(self):
+        return self
+
+    def __len__(self):
+        return max(self.total_count, 0)
+
+    def __next__(self):
+        if self.counter == self.total_count:
+            self.scheduler.drain()
+            self.node_distributor.reset()
+            self.counter = 0
+            raise StopIteration
+        # the scheduler must not start distributing a batch that does not exist
+        is_last_iter = self.counter + 1 >= self.total_count
+        seeds_cpu = self.scheduler.run(is_last_iter)
+        self.counter += 1
+        if self._seed_pin is not None:
+            self._seed_pin.copy_(seeds_cpu)
+            self._seed_buf.copy_(self._seed_pin, non_blocking=True)
+            distributed_index = self._seed_buf
+        else:
+            distributed_index = seeds_cpu.to(self.device)
+        if not self.fused:
+            batch = self.sampler.sample(self.g, distributed_index)
+            return self.COALA_GNN_Manager.fetch_feature(batch)
+        # sample and gather are enqueued back to back on one stream: the gather reads the sampler's
+        # input-node list and its length straight from device memory
+        stream = torch.cuda.current_stream().cuda_stream
+        self.sampler.sample_async(self.g, distributed_index, None, stream)
+        idx_ptr, n_ptr = self.sampler.input_nodes_dev_ptrs()
+        mgr = self.COALA_GNN_Manager
+        out = mgr.fetch_feature_async(idx_ptr, mgr.max_sample_size, n_ptr, stream)
+        input_nodes, output_nodes, blocks = self.sampler.collect()
+        return input_nodes, output_nodes, blocks, out[:input_nodes.numel()]
+
+    def print_stats(self):
+        self.COALA_GNN_Manager.print_stats()
+        agg_time = self.COALA_GNN_Manager.get_aggregate_time()
+        print(f"Aggregation time: {agg_time}")
+        self.COALA_GNN_Manager.aggregation_timer = 0.0

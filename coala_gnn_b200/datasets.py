@@ -1,0 +1,88 @@
+"""Synthetic stand-in for IGBDatast_Shared_CSC_UVA / OGBDataset_Shared_CSC_UVA
+(examples/ssd_gnn_dataloader.py:365-569, 687-854): feature table and CSC arrays live in POSIX
+shared memory, pinned and device-mapped by every rank of the machine; local rank 0 fills them.
+Differences: nothing is read from disk (shapes in synth.SHAPES), the graph is generated straight
+into the shared segments (no rank-0 np.load + second copy), and the feature table is written by a
+GPU kernel through the UVA mapping."""
+import os
+import tempfile
+import time
+
+import numpy as np
+import torch
+
+from . import synth
+from ._lib import lib, check
+from .comm import Shared_UVA_Tensor_Manager
+from .sampler import UVAGraph
+
+
+class SyntheticSharedCSCUVA(object):
+    def __init__(self, shape, comm_manager, device, num_classes=19, num_colors=None, feat_cpu=True, tag=None, verbose=False):
+        n, e, dim, gseed, fseed = synth.SHAPES[shape] if isinstance(shape, str) else shape
+        self.num_nodes, self.num_edges, self.dim, self.feat_seed = n, e, dim, fseed
+        self.comm = comm_manager
+        self.device = device
+        cd = lib().coala_cache_dim_for(dim)
+        self.cache_dim = cd
+        tag = tag or os.environ.get("MASTER_PORT", str(os.getpid()))
+        rank0 = comm_manager.local_rank == 0
+        t0 = time.time()
+
+        def seg(name, nbytes, zero=False):
+            return Shared_UVA_Tensor_Manager(comm_manager, "/coala_b200_%s_%s" % (tag, name), nbytes, zero=zero)
+
+        self.feat_data = None
+        self._segs = []
+        if feat_cpu:  # --feat_cpu: features pinned in host memory, row stride = cache_dim floats
+            m = seg("feat", n * cd * 4)
+            self._segs.append(m)
+            self.feat_data = m.get_tensor(np.float32, device, (n, cd))
+            if rank0:
+                check(lib().coala_synth_fill_features(self.feat_data.data_ptr(), fseed, 0, n, dim, cd, None))
+                torch.cuda.synchronize()
+            comm_manager.local_comm.Barrier()
+        t_feat = time.time() - t0
+        m1, m2, m3 = seg("indptr", (n + 1) * 8), seg("indices", e * 8), seg("eids", e * 8)
+        self._segs += [m1, m2, m3]
+        if rank0:
+            out = (m1.get_host_array(np.int64, (n + 1,)), m2.get_host_array(np.int64, (e,)), m3.get_host_array(np.int64, (e,)))
+            synth.make_csc(n, e, gseed, out=out, edge_ids="arange" if e > 50_000_000 else "perm")
+        comm_manager.local_comm.Barrier()
+        self.csc_host = (m1.get_host_array(np.int64, (n + 1,)), m2.get_host_array(np.int64, (e,)), m3.get_host_array(np.int64, (e,)))
+        indptr = m1.get_tensor(np.int64, device, (n + 1,))
+        indices = m2.get_tensor(np.int64, device, (e,))
+        eids = m3.get_tensor(np.int64, device, (e,))
+        self.graph = UVAGraph(indptr, indices, eids, n, device)  # dgl.graph(('csc', ...)) (:523)
+        labels = torch.from_numpy(synth.make_labels(n, num_classes, gseed)).to(device)
+        self.graph.ndata["label"] = self.graph.ndata["labels"] = labels
+        n_train, n_val = int(n * 0.6), int(n * 0.2)  # (:546-557)
+        for name, lo, hi in (("train_mask", 0, n_train), ("val_mask", n_train, n_train + n_val), ("test_mask", n_train + n_val, n)):
+            mask = torch.zeros(n, dtype=torch.bool, device=device)
+            mask[lo:hi] = True
+            self.graph.ndata[name] = mask
+        # colour metadata files in the reference's on-disk layout
+        self.meta_dir = os.path.join(tempfile.gettempdir(), "coala_b200_%s_meta" % tag)
+        if rank0:
+            os.makedirs(self.meta_dir, exist_ok=True)
+            C = num_colors or max(16, int(0.005 * n))
+            color, topk, score = synth.block_color_meta(n, C)
+            np.save(os.path.join(self.meta_dir, "color.npy"), color)
+            np.save(os.path.join(self.meta_dir, "topk.npy"), topk)
+            np.save(os.path.join(self.meta_dir, "score.npy"), score)
+        comm_manager.local_comm.Barrier()
+        self.color_file, self.topk_file, self.score_file = (os.path.join(self.meta_dir, x) for x in ("color.npy", "topk.npy", "score.npy"))
+        if verbose and comm_manager.global_rank == 0:
+            print("dataset %s ready in %.1fs (features %.1fs)" % (shape, time.time() - t0, t_feat), flush=True)
+
+    def feat_host_array(self):
+        """numpy view of the pinned feature table (host side) — used by the CPU baseline only."""
+        return self._segs[0].get_host_array(np.float32, (self.num_nodes, self.cache_dim))
+
+    def __getitem__(self, i):
+        return self.graph
+
+    def cleanup(self):
+        for m in self._segs:
+            m.cleanup()
+        self._segs = []

@@ -48,14 +48,14 @@ class SharedUVAManager:
     COALA_GNN.MPI_Comm_Manager.local_comm) — rank 0 creates the segment, the others open it
     after the barrier, as the reference does with MPI_Barrier (:65-81)."""
 
-    def __init__(self, shm_path, shm_size, node_id=0, global_comm_ptr=0, local_comm_ptr=0, device=None):
+    def __init__(self, shm_path, shm_size, node_id=0, global_comm_ptr=0, local_comm_ptr=0, device=None, zero=True):
         import torch
         comm = local_comm_ptr if hasattr(local_comm_ptr, "barrier") else None
         rank = comm.rank() if comm else 0
         dev = torch.cuda.current_device() if device is None else device
         self._path = shm_path.encode()
         if rank == 0:
-            self._h = check_handle(lib().coala_uva_create(self._path, int(shm_size), 1, dev, 1), "SharedUVAManager")
+            self._h = check_handle(lib().coala_uva_create(self._path, int(shm_size), 1, dev, 1 if zero else 0), "SharedUVAManager")
             if comm:
                 comm.barrier()
         else:

@@ -20,42 +20,74 @@ SHAPES = {
 }
 
 
-def make_csc(num_nodes, num_edges, seed, local_frac=0.8, window=4096):
-    """CSC graph with a skewed in-degree distribution (>=10% rows with deg<=5, heavy tail)
-    and community structure (``local_frac`` of in-neighbours fall within +-``window`` ids, the
-    rest follow a popularity-skewed global draw) so colour affinity is meaningful.
-    Returns (indptr int64[N+1], indices int64[E], edge_ids int64[E])."""
-    rng = np.random.default_rng(seed)
+def _degrees(num_nodes, num_edges, rng):
     mean = num_edges / num_nodes
     sigma = 1.0
     raw = rng.lognormal(mean=np.log(mean) - sigma * sigma / 2, sigma=sigma, size=num_nodes)
     deg = np.floor(raw).astype(np.int64)
-    # fix the total to exactly num_edges
-    diff = int(num_edges - deg.sum())
+    diff = int(num_edges - deg.sum())  # fix the total to exactly num_edges
     if diff > 0:
-        add = rng.integers(0, num_nodes, size=diff)
-        np.add.at(deg, add, 1)
-    elif diff < 0:
-        diff = -diff
-        while diff > 0:
-            cand = rng.integers(0, num_nodes, size=diff * 2)
-            cand = cand[deg[cand] > 0][:diff]
-            cand = np.unique(cand)
-            deg[cand] -= 1
-            diff -= len(cand)
-    indptr = np.zeros(num_nodes + 1, dtype=np.int64)
+        np.add.at(deg, rng.integers(0, num_nodes, size=diff), 1)
+    while diff < 0:
+        cand = np.unique(rng.integers(0, num_nodes, size=-diff * 2))
+        cand = cand[deg[cand] > 0][:-diff]
+        deg[cand] -= 1
+        diff += len(cand)
+    return deg
+
+
+def make_csc(num_nodes, num_edges, seed, local_frac=0.8, window=4096, out=None, chunk=1 << 20, edge_ids="perm"):
+    """CSC graph with a skewed in-degree distribution (>=10% rows with deg<=5, heavy tail)
+    and community structure (``local_frac`` of in-neighbours fall within +-``window`` ids, the
+    rest follow a popularity-skewed global draw) so colour affinity is meaningful.
+    Generated in row chunks so the 120M-edge shapes need no E-sized temporaries; `out` may hold
+    preallocated (indptr, indices, edge_ids) arrays (e.g. views of shared pinned memory).
+    edge_ids: "perm" (random permutation, small graphs), "arange", or None.
+    Returns (indptr int64[N+1], indices int64[E], edge_ids int64[E] | None)."""
+    rng = np.random.default_rng(seed)
+    deg = _degrees(num_nodes, num_edges, rng)
+    if out is not None:
+        indptr, indices, eids = out
+    else:
+        indptr = np.empty(num_nodes + 1, dtype=np.int64)
+        indices = np.empty(num_edges, dtype=np.int64)
+        eids = np.empty(num_edges, dtype=np.int64) if edge_ids else None
+    indptr[0] = 0
     np.cumsum(deg, out=indptr[1:])
-    E = int(indptr[-1])
-    dst = np.repeat(np.arange(num_nodes, dtype=np.int64), deg)
-    is_local = rng.random(E) < local_frac
-    off = rng.integers(-window, window + 1, size=E)
-    local = np.clip(dst + off, 0, num_nodes - 1)
-    u = rng.random(E)
-    glob = np.minimum((u * u * u * num_nodes).astype(np.int64), num_nodes - 1)  # skew to low ids
-    indices = np.where(is_local, local, glob).astype(np.int64)
-    del dst, is_local, off, local, u, glob
-    edge_ids = rng.permutation(E).astype(np.int64) if E <= 50_000_000 else np.arange(E, dtype=np.int64)
-    return indptr, indices, edge_ids
+    for lo in range(0, num_nodes, chunk):
+        hi = min(lo + chunk, num_nodes)
+        crng = np.random.default_rng([seed, lo])
+        e0, e1 = int(indptr[lo]), int(indptr[hi])
+        n_e = e1 - e0
+        dst = np.repeat(np.arange(lo, hi, dtype=np.int64), deg[lo:hi])
+        local = np.clip(dst + crng.integers(-window, window + 1, size=n_e), 0, num_nodes - 1)
+        u = crng.random(n_e)
+        glob = np.minimum((u * u * u * num_nodes).astype(np.int64), num_nodes - 1)  # skew to low ids
+        indices[e0:e1] = np.where(crng.random(n_e) < local_frac, local, glob)
+    if eids is not None:
+        if edge_ids == "perm" and num_edges <= 50_000_000:
+            eids[:] = rng.permutation(num_edges)
+        else:
+            for lo in range(0, num_edges, 1 << 24):
+                hi = min(lo + (1 << 24), num_edges)
+                eids[lo:hi] = np.arange(lo, hi, dtype=np.int64)
+    return indptr, indices, eids
+
+
+def block_color_meta(num_nodes, num_colors, K=10):
+    """Cheap stand-in colouring for the big shapes (the real colouring is single-threaded host
+    code, minutes at 10M nodes): colour = contiguous id block (communities are id-local in
+    make_csc), top-k = the nearest blocks with geometrically decaying affinity. Same on-disk
+    layout and quirks (1-based ids, last row zero) as the reference's tables."""
+    color = (np.arange(num_nodes, dtype=np.int64) * num_colors // num_nodes) + 1
+    base = np.arange(1, num_colors + 1, dtype=np.int64)[:, None]
+    offs = np.array([(k // 2 + 1) * (1 if k % 2 == 0 else -1) for k in range(K)], dtype=np.int64)[None, :]
+    topk = base + offs
+    topk[(topk < 1) | (topk > num_colors)] = 0
+    score = np.where(topk != 0, 0.25 * 0.7 ** (np.abs(offs) - 1), 0.0).astype(np.float64)
+    topk[-1, :] = 0
+    score[-1, :] = 0.0
+    return color, topk, score
 
 
 def make_labels(num_nodes, num_classes, seed):

@@ -1,0 +1,66 @@
+"""End-to-end GPU test of the drop-in boundary: COALA_GNN_DataLoader over the three cache
+backends on one GPU — the invariant the reference states itself
+(examples/nvshmem_homogeneous_train.py:186-198): feat[i] == feature_table[input_nodes[i]]."""
+import numpy as np
+import pytest
+
+import oracle
+from coala_gnn_b200 import synth
+
+pytestmark = pytest.mark.gpu
+
+
+def _dataset(tmp_path, n=20000, e=240000, dim=128):
+    import torch
+    from COALA_GNN import MPI_Comm_Manager, UVAGraph
+    from coala_gnn_b200.pybind import tensor_from_ptr
+    indptr, indices, eids = synth.make_csc(n, e, 7)
+    col = np.load(__import__("os").path.join(__import__("conftest").GOLDEN, "coloring_20k.npz"))
+    assert int(col["n"]) == n  # not the same graph seed, but a valid colour table for n nodes
+    cf, tf, sf = (str(tmp_path / x) for x in ("color.npy", "topk.npy", "score.npy"))
+    np.save(cf, col["color"]), np.save(tf, col["topk"]), np.save(sf, col["score"])
+    comm = MPI_Comm_Manager(0)
+    keep = []
+
+    def uva(a):
+        h = torch.from_numpy(a).pin_memory()
+        keep.append(h)
+        return tensor_from_ptr(h.data_ptr(), a.shape, str(a.dtype), "cuda:0", owner=h)
+    g = UVAGraph(uva(indptr), uva(indices), uva(eids), n, "cuda:0")
+    labels = synth.make_labels(n, 19, 1)
+    g.ndata["labels"] = g.ndata["label"] = torch.from_numpy(labels).cuda()
+    feat = oracle.fill_features(n, dim, 17)
+    feat_uva = uva(feat)
+    return dict(comm=comm, g=g, feat=feat, feat_uva=feat_uva, files=(cf, tf, sf), csc=(indptr, indices, eids), labels=labels, n=n, dim=dim)
+
+
+@pytest.mark.parametrize("backend", ["isolated", "nvshmem", "nccl"])
+@pytest.mark.parametrize("distribution", ["node_color", "baseline"])
+def test_dataloader_iterates_with_bit_exact_features(tmp_path, backend, distribution):
+    import torch
+    from COALA_GNN import Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
+    d = _dataset(tmp_path)
+    B, fan = 128, [5, 5]
+    train = torch.from_numpy(synth.train_ids(d["n"], seed=1))
+    nd = Node_Distributor(d["comm"], train, B, *d["files"], parsing_method=distribution)
+    sampler = MultiLayerNeighborSampler(fan, seed=5)
+    loader = COALA_GNN_DataLoader(SSD_INFO(1, 512, 1024, 0), nd, d["g"], sampler, B, d["dim"], fan, 2, "cuda:0",
+                                  refresh_counter=3, cache_backend=backend, sim_buf=d["feat_uva"])
+    indptr, indices, eids = d["csc"]
+    for epoch in range(2):
+        steps = 0
+        for step, (input_nodes, seeds, blocks, feat) in enumerate(loader):
+            seeds_h = seeds.cpu().numpy()
+            assert np.array_equal(seeds_h, train.numpy()[step * B:(step + 1) * B])  # one domain: in-order striping
+            inp = input_nodes.cpu().numpy()
+            assert np.array_equal(feat.cpu().numpy().view(np.uint32), d["feat"][inp].view(np.uint32))
+            einp, _, eblocks = oracle.sample_blocks_detailed(indptr, indices, eids, seeds_h, fan,
+                                                             oracle.batch_key(5, epoch * len(loader) + step))
+            assert np.array_equal(inp, einp)
+            assert np.array_equal(blocks[0].edge_src.cpu().numpy(), eblocks[0]["edge_src"])
+            assert np.array_equal(blocks[-1].dstdata["labels"].cpu().numpy(), d["labels"][seeds_h])
+            steps += 1
+        assert steps == len(loader) == len(train) // B - 1
+    h, m, b = loader.COALA_GNN_Manager.COALA_GNN_Cache.stats()
+    assert h > 0 and m > 0 and h + m + b > 0
+    loader.print_stats()
