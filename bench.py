@@ -45,6 +45,8 @@ def parse_args():
     p.add_argument("--prewarm_seconds", type=float, default=25.0)
     p.add_argument("--cpu_baseline_seconds", type=float, default=12.0)
     p.add_argument("--no_cpu_baseline", action="store_true")
+    p.add_argument("--cuda_profiler_range", action="store_true",
+                   help="bracket the timed region with cudaProfilerStart/Stop (for `ncu --profile-from-start off`)")
     return p.parse_args()
 
 
@@ -208,9 +210,14 @@ def run_ours(args):
     pipe.events.clear()
     clocks = ClockSampler(comm.device_index) if comm.global_rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if args.cuda_profiler_range:
+        torch.cuda.profiler.start()
     e0.record()
     pipe_steps(args.steps)
     e1.record()
+    if args.cuda_profiler_range:
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
     barrier_sync(comm)
     dev_ms = max_over_ranks(comm, e0.elapsed_time(e1), device)
     clk = clocks.stop() if clocks else None
