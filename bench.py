@@ -186,9 +186,7 @@ def run_ours(args):
 
     def pipe_steps(n):
         for _ in range(n):
-            if pipe.step_idx % spe == spe - 1:
-                pipe.reset()
-            pipe.step()
+            pipe.step()  # epochs wrap inside the pipeline
 
     # ---- untimed cache pre-warm through the real path (steady state is what an epoch sees)
     t0 = time.time()
@@ -198,16 +196,17 @@ def run_ours(args):
         pipe_steps(50)
         torch.cuda.synchronize()
         n_pre += 50
-        if args.prewarm < 0 and time.time() - t0 > args.prewarm_seconds:
-            break
+        if args.prewarm < 0:  # every rank must leave after the same batch (the path holds collectives)
+            if max_over_ranks(comm, float(time.time() - t0 > args.prewarm_seconds), device) > 0:
+                break
     pre_stats = cache.stats(reset=True)
-    pipe.events.clear()
+    pipe.engine.gather_times.clear()
 
     # ---- value: device-resident pipeline
     pipe_steps(args.warmup)
     barrier_sync(comm)
     cache.stats(reset=True)
-    pipe.events.clear()
+    pipe.engine.gather_times.clear()
     clocks = ClockSampler(comm.device_index) if comm.global_rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if args.cuda_profiler_range:
@@ -293,6 +292,9 @@ def run_ours(args):
 
 def main():
     args = parse_args()
+    if os.environ.get("COALA_HANG_DUMP"):  # debugging aid: dump every thread's stack if the run stalls
+        import faulthandler
+        faulthandler.dump_traceback_later(int(os.environ["COALA_HANG_DUMP"]), repeat=True, exit=False)
     world = int(os.environ.get("WORLD_SIZE", 1))
     rank = int(os.environ.get("RANK", 0))
     if args.impl == "reference":

@@ -45,6 +45,7 @@ SIGNATURES = {
     "coala_cache_read_feature_serial": (_i32, [_vp, _u64, _u64, _i64]),
     "coala_cache_get_cache_data": (_i32, [_vp, _u64]),
     "coala_cache_get_cache_data_n": (_i32, [_vp, _u64, _i32]),
+    "coala_cache_get_cache_data_async": (_i32, [_vp, _u64, _i32, _vp]),
     "coala_cache_color_counters_dev_ptr": (_u64, [_vp]),
     "coala_cache_stats": (_i32, [_vp, _vp, _vp, _vp, _i32]),
     "coala_cache_print_stats": (_i32, [_vp]),
@@ -59,6 +60,7 @@ SIGNATURES = {
     "coala_sampler_counts": (_i32, [_vp, _vp]),
     "coala_sampler_layer_ptrs": (_i32, [_vp, _i32, _vp, _vp, _vp, _vp]),
     "coala_sampler_input_count_dev_ptr": (_u64, [_vp]),
+    "coala_lookup_edge_ids": (_i32, [_u64, _u64, _i64, _u64, _vp]),
     "coala_gc_create": (_vp, [_u64]),
     "coala_gc_destroy": (None, [_vp]),
     "coala_gc_set_adj_csc": (None, [_vp, _u64, _u64]),

@@ -58,11 +58,11 @@ class MPI_Comm_Manager(object):
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
             os.environ.setdefault("MASTER_PORT", "29500")
             backend = "cpu:gloo,cuda:nccl" if torch.cuda.is_available() else "gloo"
-            kw = {}
             if torch.cuda.is_available():
                 torch.cuda.set_device(self.device_index)
-                kw["device_id"] = torch.device("cuda", self.device_index)
-            dist.init_process_group(backend, world_size=self.global_size, rank=self.global_rank, **kw)
+            # no device_id= here: binding one makes torch create NCCL communicators eagerly and turns every
+            # later new_group() into an ncclCommSplit that non-members of a *gloo* subgroup wait in forever
+            dist.init_process_group(backend, world_size=self.global_size, rank=self.global_rank)
         if gpus_per_domain is None:
             gpus_per_domain = int(os.environ.get("COALA_GPUS_PER_DOMAIN", self.global_size))
         node = int(node)

@@ -280,6 +280,15 @@ extern "C" int coala_cache_get_cache_data_n(coala_cache* c, uint64_t dst_ptr, in
     return 0;
 }
 
+extern "C" int coala_cache_get_cache_data_async(coala_cache* c, uint64_t dst_dev_ptr, int count, void* stream) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    if (count < 0 || count > c->num_colors + 1) COALA_FAIL("get_cache_data_async: count out of range");
+    if (count == 0) return 0;
+    COALA_CUDA(cudaMemcpyAsync(reinterpret_cast<void*>(dst_dev_ptr), c->params.shard[c->params.my_slot].color_counters,
+                               (size_t)count * 4, cudaMemcpyDeviceToDevice, static_cast<cudaStream_t>(stream)));
+    return 0;
+}
+
 extern "C" int coala_cache_stats(coala_cache* c, uint64_t* hit, uint64_t* miss, uint64_t* bypass, int reset) {
     COALA_CUDA(cudaSetDevice(c->device));
     unsigned long long h[4];

@@ -137,6 +137,15 @@ __global__ void nd_assign_serial_kernel(const int64_t* __restrict__ items, int64
     if (bucket_len_out) for (int j = 0; j < D; j++) bucket_len_out[j] = len[j];
 }
 
+// D == 1: every seed scores >= 0 > -1 until the single bucket is full, and the bucket holds exactly
+// N = cap seeds, so the reference loop degenerates to out[i] = item[offset + i] (:214-218).
+__global__ void nd_single_domain_kernel(const int64_t* __restrict__ items, int cap, int64_t* __restrict__ out,
+                                        int* __restrict__ bucket_len_out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < cap) out[i] = items[i];
+    if (i == 0 && bucket_len_out) bucket_len_out[0] = cap;
+}
+
 }  // namespace
 
 // ---------------------------------------------------------------------------------------------
@@ -271,6 +280,11 @@ extern "C" int coala_nd_last_bucket_len(coala_nd* h, int* out) {
 }
 
 static int nd_launch(coala_nd* h, const int64_t* d_items, const MetaPtrs& meta, int64_t* d_out, cudaStream_t st) {
+    if (h->n_domains == 1) {
+        nd_single_domain_kernel<<<(h->cap + 255) / 256, 256, 0, st>>>(d_items, h->cap, d_out, h->d_flags + 1);
+        COALA_CUDA(cudaGetLastError());
+        return 0;
+    }
     const int64_t total = h->N * h->n_domains;
     COALA_CUDA(cudaMemsetAsync(h->d_flags, 0, (1 + ND_MAX_DOMAINS) * sizeof(int), st));
     nd_score_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_items, h->N, h->n_domains, h->K, h->d_color, h->d_topk,

@@ -67,7 +67,6 @@ __global__ void ht_reset_kernel(HashTable t) {
 
 // ---- K1: one warp per frontier node: indptr pair, picks, neighbour ids into fixed-stride slots
 __global__ void __launch_bounds__(256) sample_rows_kernel(const int64_t* __restrict__ indptr, const int64_t* __restrict__ indices,
-                                                          const int64_t* __restrict__ edge_ids,
                                                           const int64_t* __restrict__ frontier, const int64_t* __restrict__ n_front,
                                                           int fanout, uint64_t layer_key, HashTable ht,
                                                           int64_t* __restrict__ slot_src, int64_t* __restrict__ slot_eid,
@@ -130,52 +129,52 @@ __global__ void __launch_bounds__(256) sample_rows_kernel(const int64_t* __restr
         if (lane < k) {
             const int64_t e = start + mypos;
             slot_src[i * fanout + lane] = indices[e];
-            slot_eid[i * fanout + lane] = edge_ids ? edge_ids[e] : e;
+            slot_eid[i * fanout + lane] = e;  // CSC position; the edge id is looked up on demand (coala_sampler_edge_ids)
         }
         if (lane == 0) cnt[i] = k;
     }
 }
 
-// ---- single-CTA exclusive scan of int32 (frontier / edge counts are at most ~1e6 here)
+// ---- single-CTA exclusive scan of int32.  Thread t owns the contiguous chunk [t*per, (t+1)*per):
+// two sweeps over L2-resident data around one block-level scan of the 1024 chunk sums (frontier /
+// edge counts are <= ~1e6 here, so per stays small and no inter-block carry is needed).
 __global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ in, int* __restrict__ out, const int64_t* __restrict__ n_ptr,
                                                     int64_t mul, int64_t* __restrict__ total_out, const int64_t* __restrict__ add_ptr,
                                                     int64_t* __restrict__ total_plus_out) {
     __shared__ int warp_sum[32];
-    __shared__ int carry;
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int64_t n = *n_ptr * mul;
-    if (tid == 0) carry = 0;
+    const int64_t per = (n + 1023) >> 10;
+    const int64_t lo = min(n, (int64_t)tid * per), hi = min(n, lo + per);
+    int sum = 0;
+    for (int64_t i = lo; i < hi; i++) sum += in[i];
+    int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        int y = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += y;
+    }
+    if (lane == 31) warp_sum[w] = incl;
     __syncthreads();
-    for (int64_t base = 0; base < n; base += 1024) {
-        const int64_t i = base + tid;
-        int x = i < n ? in[i] : 0;
-        int incl = x;
+    if (w == 0) {
+        int sw = warp_sum[lane], si = sw;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
-            int y = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += y;
+            int y = __shfl_up_sync(0xffffffffu, si, d);
+            if (lane >= d) si += y;
         }
-        if (lane == 31) warp_sum[w] = incl;
-        __syncthreads();
-        if (w == 0) {
-            int s = warp_sum[lane], si = s;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int y = __shfl_up_sync(0xffffffffu, si, d);
-                if (lane >= d) si += y;
-            }
-            warp_sum[lane] = si - s;  // exclusive warp offsets
-        }
-        __syncthreads();
-        const int c = carry;
-        if (i < n) out[i] = c + warp_sum[w] + incl - x;
-        __syncthreads();
-        if (tid == 1023) carry = c + warp_sum[w] + incl;  // last thread holds the tile's inclusive total
-        __syncthreads();
+        warp_sum[lane] = si - sw;  // exclusive warp offsets
     }
-    if (tid == 0) {
-        if (total_out) *total_out = carry;
-        if (total_plus_out) *total_plus_out = carry + *add_ptr;
+    __syncthreads();
+    int run = warp_sum[w] + incl - sum;  // exclusive prefix of this thread's chunk
+    for (int64_t i = lo; i < hi; i++) {
+        const int x = in[i];
+        out[i] = run;
+        run += x;
+    }
+    if (tid == 1023) {  // run == grand total (chunks past n are empty)
+        if (total_out) *total_out = run;
+        if (total_plus_out) *total_plus_out = run + *add_ptr;
     }
 }
 
@@ -199,6 +198,17 @@ __global__ void compact_insert_kernel(const int64_t* __restrict__ slot_src, cons
             e_id[e] = slot_eid[t];
             ht_insert_min(ht, src, (int)(ns + e));
         }
+    }
+}
+
+// ---- on demand: edge ids of the sampled CSC positions (the reference's DGL sampler reads them
+// while sampling; the SAGE/GAT consumers never look at them, so they are fetched only when asked for)
+__global__ void edge_id_lookup_kernel(const int64_t* __restrict__ pos, const int64_t* __restrict__ n_ptr, int64_t n_host,
+                                      const int64_t* __restrict__ edge_ids, int64_t* __restrict__ out) {
+    const int64_t n = n_ptr ? *n_ptr : n_host;
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
+        const int64_t p = pos[e];
+        out[e] = edge_ids ? edge_ids[p] : p;
     }
 }
 
@@ -350,7 +360,7 @@ extern "C" int coala_sampler_sample_async(coala_sampler* s, uint64_t seeds_dev_p
         while (need < 2 * (uint64_t)s->ns_max[l + 1]) need <<= 1;
         ht.mask = need - 1;
         ht_reset_kernel<<<grid_for((int64_t)need, 1024, cap), 256, 0, st>>>(ht);
-        sample_rows_kernel<<<grid_for(s->ns_max[l], 8, cap), 256, 0, st>>>(s->indptr, s->indices, s->edge_ids, s->frontier[l], d_nf + l, f,
+        sample_rows_kernel<<<grid_for(s->ns_max[l], 8, cap), 256, 0, st>>>(s->indptr, s->indices, s->frontier[l], d_nf + l, f,
                                                                           lkey, ht, s->slot_src, s->slot_eid, s->cnt);
         scan_kernel<<<1, 1024, 0, st>>>(s->cnt, s->off, d_nf + l, 1, d_ne + l, nullptr, nullptr);
         compact_insert_kernel<<<grid_for(s->ne_max[l], 256, cap), 256, 0, st>>>(s->slot_src, s->slot_eid, s->cnt, s->off, d_nf + l, f, ht,
@@ -380,12 +390,23 @@ extern "C" int coala_sampler_counts(coala_sampler* s, int64_t* counts) {
 }
 
 extern "C" int coala_sampler_layer_ptrs(coala_sampler* s, int layer, uint64_t* src_nodes, uint64_t* edge_src, uint64_t* edge_dst,
-                                        uint64_t* edge_id) {
+                                        uint64_t* edge_pos) {
     if (layer < 0 || layer >= s->L) COALA_FAIL("sampler: layer out of range");
     const int l = s->L - 1 - layer;
     if (src_nodes) *src_nodes = (uint64_t)s->frontier[l + 1];
     if (edge_src) *edge_src = (uint64_t)s->e_src_local[l];
     if (edge_dst) *edge_dst = (uint64_t)s->e_dst[l];
-    if (edge_id) *edge_id = (uint64_t)s->e_id[l];
+    if (edge_pos) *edge_pos = (uint64_t)s->e_id[l];
+    return 0;
+}
+
+extern "C" int coala_lookup_edge_ids(uint64_t edge_ids_ptr, uint64_t pos_dev_ptr, int64_t n, uint64_t out_dev_ptr, void* stream) {
+    if (n <= 0) return 0;
+    int64_t blocks = (n + 255) / 256;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    edge_id_lookup_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        reinterpret_cast<const int64_t*>(pos_dev_ptr), nullptr, n, reinterpret_cast<const int64_t*>(edge_ids_ptr),
+        reinterpret_cast<int64_t*>(out_dev_ptr));
+    COALA_CUDA(cudaGetLastError());
     return 0;
 }

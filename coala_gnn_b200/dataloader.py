@@ -94,10 +94,15 @@ class COALA_GNN_DataLoader(object):
         self.counter = 0
         self.index_len = len(self.node_distributor.index_tensor)
         self.total_count = int(self.index_len / self.node_distributor.global_batch_size) - 1  # (:139-141)
-        # fused path: sampler output feeds the gather on the device without a host round trip
-        self.fused = cache_backend in ("nvshmem", "p2p", "isolated") and hasattr(self.sampler, "sample_async")
-        self._seed_buf = torch.empty(batch_size, dtype=torch.int64, device=device)
-        self._seed_pin = torch.empty(batch_size, dtype=torch.int64).pin_memory() if torch.cuda.is_available() else None
+        # fused path: sampler output feeds the gather on the device without a host round trip, and
+        # batch t+1 is sampled while batch t is gathered / consumed (pipeline.BatchEngine)
+        self.fused = cache_backend in ("nvshmem", "p2p", "isolated") and hasattr(self.sampler, "sample_async") \
+            and torch.cuda.is_available()
+        self.engine = None
+        if self.fused:
+            from .pipeline import BatchEngine
+            self.engine = BatchEngine(graph, graph_sampler, self.COALA_GNN_Manager, batch_size, device)
+        self._epoch_base = 0  # engine batch index of this epoch's first batch
 
     def __iter__(self):
         return self
@@ -105,34 +110,45 @@ class COALA_GNN_DataLoader(object):
     def __len__(self):
         return max(self.total_count, 0)
 
+    def _launch(self, i):
+        """Distribute (host scheduler) and enqueue sample + gather of this epoch's batch i."""
+        is_last_iter = i + 1 >= self.total_count  # the scheduler must not start distributing a batch that does not exist
+        seeds_cpu = self.scheduler.run(is_last_iter)
+
+        def seed_fn(slot, stream):
+            slot.seeds_pin.copy_(seeds_cpu)
+            slot.seeds.copy_(slot.seeds_pin, non_blocking=True)
+            return slot.seeds
+        self.engine.launch(self._epoch_base + i, seed_fn)
+        self._launched = i + 1
+
     def __next__(self):
         if self.counter == self.total_count:
             self.scheduler.drain()
             self.node_distributor.reset()
+            if self.engine is not None:
+                self._epoch_base = self.engine.launched
+                self._launched = 0
             self.counter = 0
             raise StopIteration
-        # the scheduler must not start distributing a batch that does not exist
-        is_last_iter = self.counter + 1 >= self.total_count
-        seeds_cpu = self.scheduler.run(is_last_iter)
-        self.counter += 1
-        if self._seed_pin is not None:
-            self._seed_pin.copy_(seeds_cpu)
-            self._seed_buf.copy_(self._seed_pin, non_blocking=True)
-            distributed_index = self._seed_buf
-        else:
-            distributed_index = seeds_cpu.to(self.device)
         if not self.fused:
-            batch = self.sampler.sample(self.g, distributed_index)
+            seeds_cpu = self.scheduler.run(self.counter + 1 >= self.total_count)
+            self.counter += 1
+            batch = self.sampler.sample(self.g, seeds_cpu.to(self.device))
             return self.COALA_GNN_Manager.fetch_feature(batch)
-        # sample and gather are enqueued back to back on one stream: the gather reads the sampler's
-        # input-node list and its length straight from device memory
-        stream = torch.cuda.current_stream().cuda_stream
-        self.sampler.sample_async(self.g, distributed_index, None, stream)
-        idx_ptr, n_ptr = self.sampler.input_nodes_dev_ptrs()
-        mgr = self.COALA_GNN_Manager
-        out = mgr.fetch_feature_async(idx_ptr, mgr.max_sample_size, n_ptr, stream)
-        input_nodes, output_nodes, blocks = self.sampler.collect()
-        return input_nodes, output_nodes, blocks, out[:input_nodes.numel()]
+        i = self.counter
+        eng = self.engine
+        eng.consumer_checkpoint()
+        if getattr(self, "_launched", 0) <= i:
+            self._launch(i)
+        if self._launched <= i + 1 and i + 1 < self.total_count:
+            self._launch(i + 1)  # prefetch: sampled while batch i is gathered and consumed
+        self.counter += 1
+        slot = eng.slot_of(self._epoch_base + i)
+        torch.cuda.current_stream().wait_event(slot.ev_sampled)
+        input_nodes, output_nodes, blocks = slot.sampler.collect()
+        eng.wait(self._epoch_base + i)
+        return input_nodes, output_nodes, blocks, slot.out[:input_nodes.numel()]
 
     def print_stats(self):
         self.COALA_GNN_Manager.print_stats()

@@ -86,3 +86,105 @@ class SyntheticSharedCSCUVA(object):
         for m in self._segs:
             m.cleanup()
         self._segs = []
+
+
+def _copy_npy_into(dst, path, threads=8, chunk_rows=None):
+    """Stream a .npy file into `dst` (a numpy view of shared pinned memory) without materialising it:
+    memory-map the file and copy row chunks on a few threads (numpy releases the GIL in the copy).
+    The reference has rank 0 np.load the whole file and then copy it a second time
+    (examples/ssd_gnn_dataloader.py:419-437)."""
+    from concurrent.futures import ThreadPoolExecutor
+    src = np.load(path, mmap_mode="r")
+    if src.shape[0] != dst.shape[0]:
+        raise ValueError("%s: leading dimension %d, expected %d" % (path, src.shape[0], dst.shape[0]))
+    n = src.shape[0]
+    row_bytes = max(1, src[0:1].nbytes)
+    chunk_rows = chunk_rows or max(1, (64 << 20) // row_bytes)
+
+    def work(lo):
+        hi = min(n, lo + chunk_rows)
+        if src.ndim == 2 and dst.shape[1] != src.shape[1]:
+            dst[lo:hi, :src.shape[1]] = src[lo:hi]  # rows padded to the cache row stride
+        else:
+            dst[lo:hi] = src[lo:hi]
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        list(ex.map(work, range(0, n, chunk_rows)))
+
+
+def npy_shape(path):
+    a = np.load(path, mmap_mode="r")
+    return tuple(a.shape), a.dtype
+
+
+class NpySharedCSCUVA(object):
+    """On-disk counterpart of IGBDatast_Shared_CSC_UVA (examples/ssd_gnn_dataloader.py:365-569): the
+    reference's directory layout and file names,
+        <path>/<size>/processed/paper/node_feat.npy, node_label_19.npy | node_label_2K.npy
+        <path>/<size>/processed/paper__cites__paper/csc_indptr.npy, csc_indices.npy, csc_edge_ids.npy
+        <path>/<size>/color.npy, topk.npy, score.npy          (examples/sbatch_ssd_gnn_train.py:52-60)
+    loaded straight into shared pinned memory (every rank of the machine maps the same segments)."""
+
+    def __init__(self, path, size, comm_manager, device, num_classes=19, feat_cpu=True, tag=None):
+        import os.path as osp
+        self.comm, self.device = comm_manager, device
+        root = osp.join(path, size)
+        paper, cites = osp.join(root, "processed", "paper"), osp.join(root, "processed", "paper__cites__paper")
+        tag = tag or os.environ.get("MASTER_PORT", str(os.getpid()))
+        rank0 = comm_manager.local_rank == 0
+        (n, dim), fdt = npy_shape(osp.join(paper, "node_feat.npy"))
+        if fdt != np.float32:
+            raise ValueError("node_feat.npy must be float32")
+        (np1,), _ = npy_shape(osp.join(cites, "csc_indptr.npy"))
+        (e,), _ = npy_shape(osp.join(cites, "csc_indices.npy"))
+        if np1 != n + 1:
+            raise ValueError("csc_indptr.npy has %d entries for %d nodes" % (np1, n))
+        self.num_nodes, self.num_edges, self.dim = n, e, dim
+        self.cache_dim = cd = lib().coala_cache_dim_for(dim)
+        if cd < 0:
+            raise RuntimeError("Only Feature Embedding Size less than 8KB is supported\n")
+
+        def seg(name, nbytes):
+            return Shared_UVA_Tensor_Manager(comm_manager, "/coala_b200_%s_%s" % (tag, name), nbytes, zero=False)
+        self._segs = []
+        self.feat_data = None
+        if feat_cpu:
+            m = seg("feat", n * cd * 4)
+            self._segs.append(m)
+            if rank0:
+                host = m.get_host_array(np.float32, (n, cd))
+                if cd != dim:
+                    host[:, dim:] = 0
+                _copy_npy_into(host, osp.join(paper, "node_feat.npy"))
+            comm_manager.local_comm.Barrier()
+            self.feat_data = m.get_tensor(np.float32, device, (n, cd))
+        arrays = []
+        for name, fname, count in (("indptr", "csc_indptr.npy", n + 1), ("indices", "csc_indices.npy", e), ("eids", "csc_edge_ids.npy", e)):
+            m = seg(name, count * 8)
+            self._segs.append(m)
+            if rank0:
+                _copy_npy_into(m.get_host_array(np.int64, (count,)), osp.join(cites, fname))
+            arrays.append(m)
+        comm_manager.local_comm.Barrier()
+        self.csc_host = tuple(m.get_host_array(np.int64, (c,)) for m, c in zip(arrays, (n + 1, e, e)))
+        indptr, indices, eids = (m.get_tensor(np.int64, device, (c,)) for m, c in zip(arrays, (n + 1, e, e)))
+        self.graph = UVAGraph(indptr, indices, eids, n, device)
+        label_file = "node_label_19.npy" if num_classes == 19 else "node_label_2K.npy"
+        labels = torch.from_numpy(np.load(osp.join(paper, label_file))).to(torch.long).to(device)  # (:519)
+        self.graph.ndata["label"] = self.graph.ndata["labels"] = labels
+        n_train, n_val = int(n * 0.6), int(n * 0.2)  # (:546-557)
+        for name, lo, hi in (("train_mask", 0, n_train), ("val_mask", n_train, n_train + n_val), ("test_mask", n_train + n_val, n)):
+            mask = torch.zeros(n, dtype=torch.bool, device=device)
+            mask[lo:hi] = True
+            self.graph.ndata[name] = mask
+        self.color_file, self.topk_file, self.score_file = (osp.join(root, x) for x in ("color.npy", "topk.npy", "score.npy"))
+
+    def feat_host_array(self):
+        return self._segs[0].get_host_array(np.float32, (self.num_nodes, self.cache_dim))
+
+    def __getitem__(self, i):
+        return self.graph
+
+    def cleanup(self):
+        for m in self._segs:
+            m.cleanup()
+        self._segs = []

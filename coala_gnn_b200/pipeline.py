@@ -1,82 +1,173 @@
-"""Device-resident form of the mini-batch path (B200-first addition next to the drop-in loader).
+"""Two-stream execution of the mini-batch path (B200-first addition behind the drop-in loader).
 
 The reference serialises, per batch: CPU distributor (thread) -> gloo broadcast -> seeds H2D ->
-DGL sampling with host syncs -> gather (S/COALA_GNN_DataLoader.py:149-167).  Here the three stages
-are enqueued back to back on one CUDA stream and nothing returns to the host between them:
-  * every rank of a cache domain runs the (deterministic) GPU distributor on the same inputs and
-    takes its own slice, so there is no seed broadcast at all;
-  * the sampler reads its seeds from the distributor's device output, the gather reads the
-    sampler's input-node list and its length from device memory;
-  * cache colour histograms are summed across the domain with one small NCCL all-reduce every
-    `refresh_counter` batches and stay on the device.
-Results of step t are valid after `sync()`; buffers are double-buffered across steps."""
-import ctypes as C
+DGL sampling with host syncs -> gather (S/COALA_GNN_DataLoader.py:149-167).  Here a mini-batch is
+two enqueued stages on two CUDA streams and nothing returns to the host between them:
 
+  stream `sample` : [seed distribution ->] multi-layer UVA sampling + to_block   (host-link LATENCY bound)
+  stream `gather` : cached feature gather of the sampler's input-node list        (host-link / NVLink / HBM BANDWIDTH bound)
+
+Batch t+1 is launched while batch t is being gathered, so the sampler's dependent host round
+trips hide behind the gather's bulk traffic (they load different resources of the same links).
+Two slots (sampler buffers, seed buffer, output rows) alternate; events order slot reuse:
+a slot is rewritten only after its previous gather finished and the consumer moved on.
+
+`BatchEngine` is shared by the drop-in iterator (`COALA_GNN_DataLoader`, seeds come from the host
+scheduler) and by `DevicePipeline` (seeds come from the GPU distributor, no host data at all).
+"""
 import torch
 import torch.distributed as dist
 
 from ._lib import lib, check
+from .sampler import MultiLayerNeighborSampler, batch_key
+
+
+class _Slot(object):
+    def __init__(self, k, fanouts, batch_size, out, device):
+        self.k = k
+        self.sampler = MultiLayerNeighborSampler(fanouts)
+        self.seeds = torch.zeros(batch_size, dtype=torch.int64, device=device)
+        self.seeds_pin = torch.zeros(batch_size, dtype=torch.int64).pin_memory()
+        self.out = out
+        self.ev_sampled = torch.cuda.Event()
+        self.ev_gathered = torch.cuda.Event()
+        self.t0 = torch.cuda.Event(enable_timing=True)
+        self.t1 = torch.cuda.Event(enable_timing=True)
+        self.used = False
+        self.batch = -1
+
+
+class BatchEngine(object):
+    """launch(t, seed_fn) enqueues batch t; wait(t) makes the current stream wait for its rows."""
+
+    def __init__(self, graph, sampler, manager, batch_size, device, record_gather_events=False):
+        self.g, self.mgr, self.device = graph, manager, device
+        self.seed, self.rank = sampler.seed, sampler.rank
+        self.fanouts = list(sampler.fanouts)
+        self.s_sample = torch.cuda.Stream(device=device)
+        self.s_gather = torch.cuda.Stream(device=device)
+        self.ev_consumed = torch.cuda.Event()
+        self.slots = [_Slot(k, self.fanouts, batch_size, manager._out[k], device) for k in range(2)]
+        for s in self.slots:
+            s.sampler._ensure(graph, batch_size)
+        self.record = record_gather_events
+        self.gather_times = []  # (start, end) event pairs of finished launches
+        self.launched = 0
+
+    def consumer_checkpoint(self):
+        """Everything the consumer enqueued so far on the current stream precedes any slot reuse."""
+        self.ev_consumed.record(torch.cuda.current_stream())
+
+    def launch(self, t, seed_fn):
+        slot = self.slots[t & 1]
+        ss, sg = self.s_sample, self.s_gather
+        ss.wait_event(self.ev_consumed)
+        if slot.used:
+            ss.wait_event(slot.ev_gathered)  # the previous gather of this slot read the sampler's id list
+        with torch.cuda.stream(ss):
+            seeds = seed_fn(slot, ss)
+            slot.sampler.sample_async(self.g, seeds, batch_key(self.seed, t, self.rank), ss.cuda_stream)
+            slot.ev_sampled.record(ss)
+        sg.wait_event(slot.ev_sampled)
+        sg.wait_event(self.ev_consumed)      # the rows of batch t-2 (same buffer) are no longer needed
+        idx_ptr, n_ptr = slot.sampler.input_nodes_dev_ptrs()
+        with torch.cuda.stream(sg):
+            if self.record:
+                if slot.used:
+                    self.gather_times.append((slot.t0, slot.t1))
+                    slot.t0, slot.t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                slot.t0.record(sg)
+            self.mgr.COALA_GNN_Cache.read_feature_async(slot.out.data_ptr(), idx_ptr, self.mgr.max_sample_size, n_ptr, sg.cuda_stream)
+            if self.record:
+                slot.t1.record(sg)
+            slot.ev_gathered.record(sg)
+        slot.used, slot.batch = True, t
+        self.launched = t + 1
+        return slot
+
+    def slot_of(self, t):
+        slot = self.slots[t & 1]
+        assert slot.batch == t, "batch %d is not in flight" % t
+        return slot
+
+    def wait(self, t):
+        slot = self.slot_of(t)
+        torch.cuda.current_stream().wait_event(slot.ev_gathered)
+        return slot
+
+    def gather_ms(self):
+        torch.cuda.synchronize()
+        return [a.elapsed_time(b) for a, b in self.gather_times]
 
 
 class DevicePipeline(object):
-    def __init__(self, loader, record_gather_events=False):
+    """Device-resident form of the path for one cache domain: every rank of the domain runs the
+    (deterministic) GPU distributor on the same inputs and takes its own slice, so there is no seed
+    broadcast; the domain's cache colour histogram is summed with one small NCCL all-reduce every
+    `refresh_counter` batches and stays on the device.  step() returns the rows of batch t (valid on
+    the current stream) while batch t+1 is already in flight."""
+
+    def __init__(self, loader, record_gather_events=False, prefetch=True):
         self.loader = loader
         self.nd = loader.node_distributor
         self.comm = self.nd.comm_manager
         self.mgr = loader.COALA_GNN_Manager
-        self.sampler = loader.sampler
         self.g = loader.g
         self.device = loader.device
         assert self.nd._dev_index is not None, "seed list must be device resident"
         if self.comm.num_master_process != 1:
             raise NotImplementedError("DevicePipeline drives one cache domain; use the drop-in loader for D > 1")
         self.B, self.L = self.nd.batch_size, self.comm.local_size
-        self.out_seeds = [torch.zeros(self.B * self.L, dtype=torch.int64, device=self.device) for _ in range(2)]
+        self.engine = BatchEngine(self.g, loader.sampler, self.mgr, self.B, self.device, record_gather_events)
+        self.domain_seeds = [torch.zeros(self.B * self.L, dtype=torch.int64, device=self.device) for _ in range(2)]
         self.meta = torch.zeros(self.nd.meta_len, dtype=torch.int32, device=self.device)
         self.step_idx = 0
-        self.offset = 0
         self.refresh = loader.refresh_counter
-        self.events = [] if record_gather_events else None
-        self.kernels_per_step = 3 + 1 + 7 * len(self.sampler.fanouts) + 1  # distributor, set_count, sampler rounds, gather
-        self.sampler._ensure(self.g, self.B)
-
-    def refresh_meta(self):
-        """Colour histogram of the whole domain's cache -> device int32[meta_len]."""
-        cache = self.mgr.COALA_GNN_Cache
-        check(lib().coala_cache_get_cache_data_n(cache._h, self.meta.data_ptr(), self.nd.meta_len), "get_cache_data")
-        if self.L > 1:
-            dist.all_reduce(self.meta, group=self.comm.nccl_cache_gather)
-
-    def step(self):
-        stream = torch.cuda.current_stream().cuda_stream
-        if self.step_idx % self.refresh == 0 and self.step_idx > 0:
-            self.refresh_meta()
-        k = self.step_idx & 1
-        seeds_all = self.out_seeds[k]
-        if self.nd.parsing_method == "node_color":
-            self.nd.distribute_manager.distribute_async(self.offset, seeds_all.data_ptr(), [self.meta.data_ptr()], stream)
-            seeds = seeds_all[self.comm.local_rank * self.B:(self.comm.local_rank + 1) * self.B]
-        else:
-            lo = self.offset + self.comm.local_rank * self.B
-            seeds = self.nd._dev_index[lo:lo + self.B]
-        self.offset += self.nd.global_batch_size
-        self.sampler.sample_async(self.g, seeds, None, stream)
-        idx_ptr, n_ptr = self.sampler.input_nodes_dev_ptrs()
-        if self.events is not None:
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-        out = self.mgr.fetch_feature_async(idx_ptr, self.mgr.max_sample_size, n_ptr, stream)
-        if self.events is not None:
-            e1.record()
-            self.events.append((e0, e1))
-        self.step_idx += 1
-        return out
-
-    def reset(self):
-        self.offset = 0
+        self.prefetch = prefetch
+        n_dist = 1 if self.nd.parsing_method == "node_color" else 0  # D == 1: the pass-through kernel
+        self.kernels_per_step = n_dist + 1 + 7 * len(self.engine.fanouts) + 1  # + set_count, sampler rounds, gather
 
     def steps_per_epoch(self):
         return len(self.nd.index_tensor) // self.nd.global_batch_size - 1
 
+    def _seed_fn(self, t):
+        def fn(slot, stream):
+            offset = (t % self.steps_per_epoch()) * self.nd.global_batch_size
+            if t % self.refresh == 0 and t > 0:
+                self.refresh_meta(stream)
+            if self.nd.parsing_method == "node_color":
+                dom = self.domain_seeds[t & 1]
+                self.nd.distribute_manager.distribute_async(offset, dom.data_ptr(), [self.meta.data_ptr()], stream.cuda_stream)
+                return dom[self.comm.local_rank * self.B:(self.comm.local_rank + 1) * self.B]
+            lo = offset + self.comm.local_rank * self.B
+            return self.nd._dev_index[lo:lo + self.B]
+        return fn
+
+    def refresh_meta(self, stream):
+        """Colour histogram of the whole domain's cache -> device int32[meta_len] (on `stream`)."""
+        cache = self.mgr.COALA_GNN_Cache
+        check(lib().coala_cache_get_cache_data_async(cache._h, self.meta.data_ptr(), self.nd.meta_len, stream.cuda_stream), "get_cache_data")
+        if self.L > 1:
+            dist.all_reduce(self.meta, group=self.comm.nccl_cache_gather)  # runs on the current (= sample) stream
+
+    def step(self):
+        t = self.step_idx
+        eng = self.engine
+        eng.consumer_checkpoint()
+        if eng.launched <= t:
+            eng.launch(t, self._seed_fn(t))
+        if self.prefetch and eng.launched <= t + 1:
+            eng.launch(t + 1, self._seed_fn(t + 1))
+        slot = eng.wait(t)
+        self.step_idx += 1
+        return slot.out
+
+    def current_sampler(self):
+        """Sampler object holding the blocks of the batch returned by the last step()."""
+        return self.engine.slot_of(self.step_idx - 1).sampler
+
+    def reset(self):  # epochs wrap inside _seed_fn; kept for API compatibility
+        pass
+
     def gather_ms(self):
-        return [a.elapsed_time(b) for a, b in self.events]
+        return self.engine.gather_ms()

@@ -58,18 +58,53 @@ class _Frame(dict):
         return set(super().keys()) | set(self._g.ndata.keys())
 
 
+class _EdgeFrame(dict):
+    """edata: '_ID' (dgl.EID) is looked up from the graph's edge-id array on first access."""
+
+    def __init__(self, block):
+        super().__init__()
+        self._b = block
+
+    def __missing__(self, key):
+        if key != "_ID":
+            raise KeyError(key)
+        self[key] = self._b.edge_id
+        return self[key]
+
+    def keys(self):
+        return set(super().keys()) | {"_ID"}
+
+
 class Block:
     """One bipartite layer: edges (edge_src[e] -> edge_dst[e]) in local ids; dst nodes are the first
-    ``num_dst_nodes`` src nodes. srcdata['_ID'] / dstdata['_ID'] are the global node ids (dgl.NID)."""
+    ``num_dst_nodes`` src nodes. srcdata['_ID'] / dstdata['_ID'] are the global node ids (dgl.NID).
+    ``edge_pos`` are the CSC positions of the sampled edges; ``edge_id`` / edata['_ID'] (the graph's
+    edge ids at those positions) are fetched from the UVA edge-id array on first use."""
 
-    def __init__(self, graph, src_nodes, n_dst, edge_src, edge_dst, edge_id):
+    def __init__(self, graph, src_nodes, n_dst, edge_src, edge_dst, edge_pos):
+        self._g = graph
         self.src_nodes, self.dst_nodes = src_nodes, src_nodes[:n_dst]
-        self.edge_src, self.edge_dst, self.edge_id = edge_src, edge_dst, edge_id
+        self.edge_src, self.edge_dst, self.edge_pos = edge_src, edge_dst, edge_pos
+        self._edge_id = None
         self.srcdata = _Frame(graph, self.src_nodes)
         self.dstdata = _Frame(graph, self.dst_nodes)
         self.srcdata["_ID"] = self.src_nodes
         self.dstdata["_ID"] = self.dst_nodes
-        self.edata = {"_ID": edge_id}
+        self.edata = _EdgeFrame(self)
+
+    @property
+    def edge_id(self):
+        if self._edge_id is None:
+            import torch
+            eids = getattr(self._g, "edge_ids", None)
+            if eids is None:
+                self._edge_id = self.edge_pos
+            else:
+                out = torch.empty_like(self.edge_pos)
+                check(lib().coala_lookup_edge_ids(eids.data_ptr(), self.edge_pos.data_ptr(), self.edge_pos.numel(), out.data_ptr(),
+                                                  torch.cuda.current_stream().cuda_stream), "edge id lookup")
+                self._edge_id = out
+        return self._edge_id
 
     def number_of_src_nodes(self):
         return int(self.src_nodes.numel())

@@ -120,6 +120,8 @@ int coala_cache_read_feature_serial(coala_cache* c, uint64_t out_ptr, uint64_t i
 int coala_cache_get_cache_data(coala_cache* c, uint64_t dst_int32_ptr);
 /* same with an explicit entry count (<= num_colors+1) */
 int coala_cache_get_cache_data_n(coala_cache* c, uint64_t dst_int32_ptr, int count);
+/* device-to-device on `stream` (the counters stay on the GPU for the device-resident distributor) */
+int coala_cache_get_cache_data_async(coala_cache* c, uint64_t dst_dev_ptr, int count, void* stream);
 uint64_t coala_cache_color_counters_dev_ptr(coala_cache* c);
 /* print_stats (M/ssd_gnn_cache.cuh:188-190, M/nvshmem_cache.h:133-142): counters since last reset */
 int coala_cache_stats(coala_cache* c, uint64_t* hit, uint64_t* miss, uint64_t* bypass, int reset);
@@ -153,9 +155,14 @@ int coala_sampler_sample_async(coala_sampler* s, uint64_t seeds_dev_ptr, int ns,
  * reference block order (input layer first), then n_seeds */
 int coala_sampler_counts(coala_sampler* s, int64_t* counts);
 /* device addresses of layer l (reference block order): src node ids [n_src], edge_src_local [ne],
- * edge_dst_local [ne], edge ids [ne]; dst nodes of layer l are the first n_dst src nodes */
+ * edge_dst_local [ne], CSC positions of the sampled edges [ne]; dst nodes of layer l are the first
+ * n_dst src nodes */
 int coala_sampler_layer_ptrs(coala_sampler* s, int layer, uint64_t* src_nodes, uint64_t* edge_src, uint64_t* edge_dst,
-                             uint64_t* edge_id);
+                             uint64_t* edge_pos);
+/* edge ids of sampled CSC positions: out[i] = edge_ids[pos[i]] (edge_ids_ptr == 0: out[i] = pos[i]).
+ * DGL's sampler reads the edge-id array while it samples (one more host round trip per picked edge);
+ * here that lookup is deferred until a consumer asks for block.edata['_ID']. */
+int coala_lookup_edge_ids(uint64_t edge_ids_ptr, uint64_t pos_dev_ptr, int64_t n, uint64_t out_dev_ptr, void* stream);
 uint64_t coala_sampler_input_count_dev_ptr(coala_sampler* s); /* device int64: n input nodes */
 
 /* ------------------------------------------------------------------ offline colour metadata

@@ -64,3 +64,38 @@ def test_dataloader_iterates_with_bit_exact_features(tmp_path, backend, distribu
     h, m, b = loader.COALA_GNN_Manager.COALA_GNN_Cache.stats()
     assert h > 0 and m > 0 and h + m + b > 0
     loader.print_stats()
+
+
+@pytest.mark.parametrize("backend", ["isolated", "nvshmem"])
+@pytest.mark.parametrize("prefetch", [True, False])
+def test_device_pipeline_two_stream_prefetch_is_bit_exact(tmp_path, backend, prefetch):
+    """DevicePipeline (GPU distributor -> sampler -> gather on two streams, batch t+1 in flight while
+    batch t is returned): rows, input nodes and blocks of every step equal the oracle's, across an
+    epoch wrap, with slot reuse."""
+    import torch
+    from COALA_GNN import Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
+    from coala_gnn_b200.pipeline import DevicePipeline
+    d = _dataset(tmp_path)
+    B, fan = 256, [5, 5]
+    train = torch.from_numpy(synth.train_ids(d["n"], seed=1))
+    nd = Node_Distributor(d["comm"], train, B, *d["files"], parsing_method="node_color")
+    sampler = MultiLayerNeighborSampler(fan, seed=9)
+    loader = COALA_GNN_DataLoader(SSD_INFO(1, 512, 1024, 0), nd, d["g"], sampler, B, d["dim"], fan, 2, "cuda:0",
+                                  refresh_counter=4, cache_backend=backend, sim_buf=d["feat_uva"])
+    pipe = DevicePipeline(loader, record_gather_events=True, prefetch=prefetch)
+    spe = pipe.steps_per_epoch()
+    indptr, indices, eids = d["csc"]
+    n_steps = spe + 5
+    for t in range(n_steps):
+        out = pipe.step()
+        torch.cuda.current_stream().synchronize()
+        seeds = train.numpy()[(t % spe) * B:(t % spe + 1) * B]
+        einp, _, eblocks = oracle.sample_blocks_detailed(indptr, indices, eids, seeds, fan, oracle.batch_key(9, t))
+        inp, outn, blocks = pipe.current_sampler().collect()
+        assert np.array_equal(outn.cpu().numpy(), seeds)
+        assert np.array_equal(inp.cpu().numpy(), einp)
+        assert np.array_equal(blocks[0].edge_src.cpu().numpy(), eblocks[0]["edge_src"])
+        assert np.array_equal(blocks[0].edge_id.cpu().numpy(), eblocks[0]["edge_id"])
+        rows = out[:len(einp)].cpu().numpy()
+        assert np.array_equal(rows.view(np.uint32), d["feat"][einp].view(np.uint32))
+    assert len(pipe.gather_ms()) >= n_steps - 2
