@@ -45,6 +45,7 @@ def parse_args():
     p.add_argument("--prewarm_seconds", type=float, default=25.0)
     p.add_argument("--cpu_baseline_seconds", type=float, default=12.0)
     p.add_argument("--no_cpu_baseline", action="store_true")
+    p.add_argument("--profile_e2e", action="store_true", help="cProfile the host side of the e2e loop (rank 0) to stderr")
     p.add_argument("--cuda_profiler_range", action="store_true",
                    help="bracket the timed region with cudaProfilerStart/Stop (for `ncu --profile-from-start off`)")
     return p.parse_args()
@@ -181,7 +182,7 @@ def run_ours(args):
     check(lib().coala_probe_read_bandwidth(ds.feat_data.data_ptr(), min(ds.num_nodes * R, 4 << 30), 2, C.byref(gb)))
     host_peak = gb.value
 
-    pipe = DevicePipeline(loader, record_gather_events=True)
+    pipe = DevicePipeline(loader, record_gather_events=True, seed=1001)  # its own sample stream: the e2e leg must not replay these batches
     spe = pipe.steps_per_epoch()
 
     def pipe_steps(n):
@@ -201,12 +202,14 @@ def run_ours(args):
                 break
     pre_stats = cache.stats(reset=True)
     pipe.engine.gather_times.clear()
+    pipe.engine.sample_times.clear()
 
     # ---- value: device-resident pipeline
     pipe_steps(args.warmup)
     barrier_sync(comm)
     cache.stats(reset=True)
     pipe.engine.gather_times.clear()
+    pipe.engine.sample_times.clear()
     clocks = ClockSampler(comm.device_index) if comm.global_rank == 0 else None
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     if args.cuda_profiler_range:
@@ -222,6 +225,7 @@ def run_ours(args):
     clk = clocks.stop() if clocks else None
     h, m, b = cache.stats(reset=True)
     gather_ms = float(np.mean(pipe.gather_ms()))
+    sample_ms = float(np.mean(pipe.engine.sample_ms()))
     rows = (h + m + b) / args.steps
     value = N * args.steps / (dev_ms * 1e-3)
 
@@ -245,10 +249,20 @@ def run_ours(args):
     loader_steps(max(3, args.warmup // 2))
     barrier_sync(comm)
     cache.stats(reset=True)
+    prof = None
+    if args.profile_e2e and comm.global_rank == 0:
+        import cProfile
+        prof = cProfile.Profile()
+        prof.enable()
     t0 = time.perf_counter()
     loader_steps(args.steps)
     torch.cuda.synchronize()
-    e2e_s = max_over_ranks(comm, time.perf_counter() - t0, device)
+    e2e_local = time.perf_counter() - t0
+    if prof is not None:
+        import pstats
+        prof.disable()
+        pstats.Stats(prof, stream=sys.stderr).sort_stats("cumulative").print_stats(35)
+    e2e_s = max_over_ranks(comm, e2e_local, device)
     barrier_sync(comm)
     eh, em, eb = cache.stats(reset=True)
     e2e_value = N * args.steps / e2e_s
@@ -274,7 +288,7 @@ def run_ours(args):
                        "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (> 126 MB L2, no reuse between steps)" % (rows * R / 1e6),
                        "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter},
             "hit_ratio": hs / max(1.0, hs + ms_ + bs), "rows_per_step": rows,
-            "gather_GBs": rows * R / t_meas / 1e9,
+            "gather_GBs": rows * R / t_meas / 1e9, "sample_stream_ms": sample_ms,
             "roofline": {"bound": "hbm", "achieved": alg_hbm / t_meas / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": alg_hbm / t_meas / 1e9 / hbm_peak,
                          "traffic": None, "peak_source": peak_src, "kernel": "coala_gather_kernel", "kernel_ms": gather_ms,
                          "kernel_share_of_step": gather_ms / (dev_ms / args.steps),

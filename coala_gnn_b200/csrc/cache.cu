@@ -54,6 +54,10 @@ struct coala_cache {
     unsigned long long* d_stats = nullptr;
     void* ipc_mapped[COALA_MAX_GPUS] = {nullptr};
     int copy_engine = 0;
+    int waves = 2;
+    int ctas_per_sm = 2;   // residency cap of the gather (see launch_gather)
+    size_t smem_per_sm = 228 * 1024;
+    int min_blocks = 3;  // __launch_bounds__ variant of the gather kernel (resident CTAs per SM)
     int sm_count = 148, blocks_per_sm = 4;
     std::vector<int32_t> h_counters;
 };
@@ -67,18 +71,36 @@ extern "C" int coala_cache_dim_for(int dim) {
     return -1;  // "Only Feature Embedding Size less than 8KB is supported" (M/ssd_gnn_cache.cuh:43-44)
 }
 
-template <int VPL, bool SYS>
+template <int VPL, bool SYS, int MINB>
 static int launch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
                          bool serial) {
     if (n <= 0) return 0;
     if (serial) {
-        coala_gather_kernel<VPL, SYS><<<1, 32, 0, st>>>(c->params, idx, out, n, n_dev);
+        coala_gather_kernel<VPL, SYS, MINB><<<1, 32, 0, st>>>(c->params, idx, out, n, n_dev);
     } else {
+        // A fixed grid of `waves` x (resident CTAs); every warp takes one contiguous chunk of the rows
+        // (sized on the device from the real count).  Two waves by default: CTAs retire early enough
+        // for the next batch's sampling kernels (higher-priority stream) to get SM slots, and long
+        // enough for a warp to pipeline several rows.  COALA_GATHER_WAVES overrides.
+        //
+        // SM budget: the gather is bandwidth bound and saturates its link with 16 warps per SM, while the
+        // next batch's sampling kernels (other stream) are latency bound and need resident warps to keep
+        // host round trips in flight.  `ctas_per_sm` caps the gather's residency by reserving (unused)
+        // dynamic shared memory, so registers and warp slots stay free for the sampler instead of the
+        // two kernels taking turns.  COALA_GATHER_CTAS_PER_SM overrides (0 = no cap).
         const int threads = 256, wpb = threads / 32;
-        int64_t blocks = (n + wpb - 1) / wpb;
-        int64_t cap = (int64_t)c->sm_count * c->blocks_per_sm;
-        if (blocks > cap) blocks = cap;
-        coala_gather_kernel<VPL, SYS><<<(unsigned)blocks, threads, 0, st>>>(c->params, idx, out, n, n_dev);
+        int resident = MINB;
+        size_t smem = 0;
+        if (c->ctas_per_sm > 0 && c->ctas_per_sm < MINB) {
+            resident = c->ctas_per_sm;
+            smem = (size_t)(c->smem_per_sm / resident) - 2048;  // per-CTA reservation incl. the driver's 1 KB
+            // per device, and cheap: set on every launch rather than tracking (device, instantiation) pairs
+            COALA_CUDA(cudaFuncSetAttribute(coala_gather_kernel<VPL, SYS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        }
+        int64_t blocks = (int64_t)c->sm_count * resident * c->waves;
+        const int64_t need = (n + wpb - 1) / wpb;
+        if (blocks > need) blocks = need;
+        coala_gather_kernel<VPL, SYS, MINB><<<(unsigned)blocks, threads, smem, st>>>(c->params, idx, out, n, n_dev);
     }
     COALA_CUDA(cudaGetLastError());
     return 0;
@@ -88,9 +110,12 @@ static int dispatch_gather(coala_cache* c, const int64_t* idx, float* out, int64
                            bool serial) {
     const bool sys = c->kind == COALA_CACHE_PARTITIONED && c->n_gpus > 1;
     const int vpl = c->row_bytes / 512;
-#define COALA_GO(V)                                                                        \
-    return sys ? launch_gather<V, true>(c, idx, out, n, n_dev, st, serial)                 \
-               : launch_gather<V, false>(c, idx, out, n, n_dev, st, serial)
+#define COALA_GO(V)                                                                                    \
+    if (c->min_blocks == 2)                                                                            \
+        return sys ? launch_gather<V, true, 2>(c, idx, out, n, n_dev, st, serial)                      \
+                   : launch_gather<V, false, 2>(c, idx, out, n, n_dev, st, serial);                    \
+    return sys ? launch_gather<V, true, 3>(c, idx, out, n, n_dev, st, serial)                          \
+               : launch_gather<V, false, 3>(c, idx, out, n, n_dev, st, serial)
     switch (vpl) {
         case 1: COALA_GO(1);
         case 2: COALA_GO(2);
@@ -157,13 +182,15 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     p.out_stride = feat_dim;
     p.out_dim = feat_dim < cache_dim ? feat_dim : cache_dim;
     p.stats = c->d_stats;
+    p.zero = 0;
+    if (const char* e = getenv("COALA_GATHER_MINB")) c->min_blocks = atoi(e) == 2 ? 2 : 3;
+    if (const char* e = getenv("COALA_GATHER_CTAS_PER_SM")) c->ctas_per_sm = atoi(e);
+    if (const char* e = getenv("COALA_GATHER_WAVES")) c->waves = atoi(e) > 0 ? atoi(e) : 2;
 
     cudaDeviceProp prop;
     COALA_CUDA_NULL(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
-    int occ = 0;
-    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, coala_gather_kernel<8, false>, 256, 0) == cudaSuccess && occ > 0)
-        c->blocks_per_sm = occ;
+    c->smem_per_sm = prop.sharedMemPerMultiprocessor;
     COALA_CUDA_NULL(cudaDeviceSynchronize());
     return c;
 }

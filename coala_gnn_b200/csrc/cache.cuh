@@ -49,6 +49,7 @@ struct CacheParams {
     int out_stride;          // floats between output rows (= feat_dim)
     int out_dim;             // floats copied per output row (min(feat_dim, cache_dim))
     unsigned long long* stats;  // [0]=hit [1]=miss [2]=bypass
+    uint32_t zero;           // always 0 at run time; unknown to the compiler (see read_line_validated)
 };
 
 constexpr int LOCK_TRIES = 64;     // CAS attempts on a set lock before bypassing
@@ -84,36 +85,58 @@ __device__ __forceinline__ void load_host_row(const CacheParams& p, uint64_t id,
 
 // Optimistic read of `slot` whose tag word was observed as `tw` (even version, id matches).
 // Returns true when the registers hold a consistent copy of the line.
+//
+// Seqlock reader WITHOUT a fence.  A fence here is MEMBAR.ALL.{GPU,SYS} (+ an L1 invalidate for
+// every acquire load): on the hit path that is the dominant cost, and over NVLink it drains the SM.
+// Instead the three steps are chained by register dependencies, which the hardware cannot reorder:
+//   tag probe --(slot address computed from the tag)--> row loads --(address of the re-check is
+//   computed from the loaded row words, `& p.zero`)--> tag re-check.
+// All of them are strong (.relaxed.gpu/.sys) accesses that resolve at the owner's L2, the single
+// point of coherence of that memory.  The re-check is issued after every row word has returned, so
+// it observes the tag at a later time than every row read; the writer orders "tag odd -> row
+// stores -> tag even" with fences (slow path below).  If both tag observations are equal and
+// even, no writer touched the row in between.
 template <int VPL, bool SYS>
-__device__ __forceinline__ bool read_line_validated(const ShardView& sh, uint64_t slot, uint64_t tw, uint32_t row_vecs,
-                                                    uint4 (&v)[VPL], unsigned lane) {
+__device__ __forceinline__ bool read_line_validated(const CacheParams& p, const ShardView& sh, uint64_t slot, uint64_t tw,
+                                                    uint32_t row_vecs, uint4 (&v)[VPL], unsigned lane) {
     const uint4* src = sh.lines + slot * row_vecs;
 #pragma unroll
     for (int k = 0; k < VPL; k++) v[k] = ld_line_v4<SYS>(src + k * 32 + lane);
-    fence_acq_rel<SYS>();  // order the row loads before the re-check (seqlock reader)
-    uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + slot);
-    return t2 == tw;  // warp-uniform: every lane loads the same word
+    uint32_t acc = 0;
+#pragma unroll
+    for (int k = 0; k < VPL; k++) acc |= v[k].x | v[k].y | v[k].z | v[k].w;
+    const uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + slot + (acc & p.zero));
+    return __all_sync(0xffffffffu, t2 == tw);
 }
 
 // One warp resolves one node id. Returns 0 hit, 1 miss (filled), 2 bypass.
+// `g`/`set` locate the id (owner shard, set); `t` is this lane's tag of that set, probed earlier
+// (prefetched while the previous row was in flight).
 template <int VPL, bool SYS>
-__device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, float* out_row, unsigned lane) {
-    const int g = p.route_gpus > 1 ? (int)(id % (uint64_t)p.route_gpus) : p.my_slot;
+__device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, int g, uint64_t set, uint64_t t,
+                                           float* out_row, unsigned lane) {
     const ShardView& sh = p.shard[g];
-    const uint64_t set = (id / (uint64_t)p.hash_div) % p.num_sets;
     const uint64_t slot0 = set * COALA_WAYS;
     const uint32_t row_vecs = p.row_bytes >> 4;
     uint4 v[VPL];
 
-    // ---- fast path: probe 32 tags with one coalesced 256-B access
-    uint64_t t = ld_acquire_u64<SYS>(sh.tags + slot0 + lane);
+    // ---- fast path: 32 tags were probed with one coalesced 256-B access
     unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
     if (m) {
         int way = __ffs(m) - 1;
         uint64_t tw = __shfl_sync(0xffffffffu, t, way);
-        if (((tw >> TAG_VER_SHIFT) & 1) == 0 && read_line_validated<VPL, SYS>(sh, slot0 + way, tw, row_vecs, v, lane)) {
+        if (((tw >> TAG_VER_SHIFT) & 1) == 0) {
+            // the row is written out before it is validated (the re-check's latency then overlaps the
+            // next row's loads); a failed validation falls through and the slow path rewrites the row
+            const uint4* src = sh.lines + (slot0 + way) * row_vecs;
+#pragma unroll
+            for (int k = 0; k < VPL; k++) v[k] = ld_line_v4<SYS>(src + k * 32 + lane);
             store_out_row<VPL>(p, out_row, v, lane);
-            return 0;
+            uint32_t acc = 0;
+#pragma unroll
+            for (int k = 0; k < VPL; k++) acc |= v[k].x | v[k].y | v[k].z | v[k].w;
+            const uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + slot0 + way + (acc & p.zero));
+            if (__all_sync(0xffffffffu, t2 == tw)) return 0;
         }
     }
 
@@ -125,6 +148,7 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, fl
     bool locked = false;
     if (lane == 0) {
         unsigned ns = 32;
+#pragma unroll 1
         for (int tries = 0; tries < LOCK_TRIES; tries++) {
             s = ld_relaxed_u64<SYS>(sh.set_seq + set);
             if ((s & 1) == 0 && cas_acquire_u64<SYS>(sh.set_seq + set, s, s + 1) == s) { locked = true; break; }
@@ -149,10 +173,11 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, fl
         int way = __ffs(m) - 1;
         const uint64_t slot = slot0 + way;
         uint64_t tw = __shfl_sync(0xffffffffu, t, way);
+#pragma unroll 1
         for (int poll = 0; poll < BUSY_POLLS; poll++) {
             if ((tw & TAG_ID_MASK) != id) break;  // evicted again meanwhile
             if (((tw >> TAG_VER_SHIFT) & 1) == 0) {
-                if (read_line_validated<VPL, SYS>(sh, slot, tw, row_vecs, v, lane)) {
+                if (read_line_validated<VPL, SYS>(p, sh, slot, tw, row_vecs, v, lane)) {
                     store_out_row<VPL>(p, out_row, v, lane);
                     return 0;
                 }
@@ -203,8 +228,14 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, fl
     return 1;
 }
 
-template <int VPL, bool SYS>
-__global__ void __launch_bounds__(256) coala_gather_kernel(CacheParams p, const int64_t* __restrict__ idx,
+// Work split: the rows are cut into one contiguous chunk per warp from the DEVICE-side row count,
+// so the same launch shape serves any n (the count comes from the sampler and never visits the
+// host).  Within a chunk lane l owns row l's id and does the 64-bit owner/set arithmetic for it
+// once; ids, owners and sets are then broadcast by shuffle, and the tag probe of row i+1 is issued
+// before row i is copied, so a warp's rows overlap instead of paying idx -> tag -> row -> re-check
+// latencies back to back.
+template <int VPL, bool SYS, int MINB>
+__global__ void __launch_bounds__(256, MINB) coala_gather_kernel(CacheParams p, const int64_t* __restrict__ idx,
                                                            float* __restrict__ out, int64_t n,
                                                            const int64_t* __restrict__ n_dev) {
     __shared__ unsigned s_stat[3];
@@ -213,13 +244,40 @@ __global__ void __launch_bounds__(256) coala_gather_kernel(CacheParams p, const 
     if (n_dev) n = min(n, *n_dev);
     const unsigned lane = lane_id();
     const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t rpw = (n + warps_total - 1) / warps_total;
+    const int64_t end = min(n, (w + 1) * rpw);
     unsigned n_hit = 0, n_miss = 0, n_byp = 0;
-    for (int64_t r = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5); r < n; r += warps_total) {
-        const uint64_t id = (uint64_t)__ldg(idx + r);
-        int res = resolve_row<VPL, SYS>(p, id, out + r * (int64_t)p.out_stride, lane);
-        n_hit += res == 0;
-        n_miss += res == 1;
-        n_byp += res == 2;
+    for (int64_t base = w * rpw; base < end; base += 32) {
+        const int cnt = (int)min((int64_t)32, end - base);
+        uint64_t my_id = 0;
+        int my_g = p.my_slot;
+        uint32_t my_set = 0;
+        if ((int)lane < cnt) {
+            my_id = (uint64_t)__ldg(idx + base + lane);
+            if (p.route_gpus > 1) my_g = (int)(my_id % (uint64_t)p.route_gpus);
+            my_set = (uint32_t)((my_id / (uint64_t)p.hash_div) % p.num_sets);
+        }
+        uint64_t id = __shfl_sync(0xffffffffu, my_id, 0);
+        int g = __shfl_sync(0xffffffffu, my_g, 0);
+        uint32_t set = __shfl_sync(0xffffffffu, my_set, 0);
+        uint64_t t = ld_relaxed_u64<SYS>(p.shard[g].tags + (uint64_t)set * COALA_WAYS + lane);
+        for (int i = 0; i < cnt; i++) {
+            uint64_t id_n = 0, t_n = 0;
+            int g_n = 0;
+            uint32_t set_n = 0;
+            if (i + 1 < cnt) {
+                id_n = __shfl_sync(0xffffffffu, my_id, i + 1);
+                g_n = __shfl_sync(0xffffffffu, my_g, i + 1);
+                set_n = __shfl_sync(0xffffffffu, my_set, i + 1);
+                t_n = ld_relaxed_u64<SYS>(p.shard[g_n].tags + (uint64_t)set_n * COALA_WAYS + lane);
+            }
+            const int res = resolve_row<VPL, SYS>(p, id, g, set, t, out + (base + i) * (int64_t)p.out_stride, lane);
+            n_hit += res == 0;
+            n_miss += res == 1;
+            n_byp += res == 2;
+            id = id_n; g = g_n; set = set_n; t = t_n;
+        }
     }
     if (lane == 0) {
         if (n_hit) atomicAdd(&s_stat[0], n_hit);

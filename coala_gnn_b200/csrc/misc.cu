@@ -174,3 +174,53 @@ extern "C" int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int i
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
     return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// random small-read probe: how many independent locations per second a link serves when every
+// location is read as `span` contiguous bytes (8, 32, 64, 128 or 256) by neighbouring lanes.  Tells whether
+// the link charges per request or per 32-byte sector — the design input of the UVA sampler.
+// ------------------------------------------------------------------------------------------
+__global__ void probe_random_kernel(const uint64_t* __restrict__ src, uint64_t n_lines, int lanes_per_loc, int iters,
+                                    uint64_t seed, int misalign, unsigned long long* __restrict__ sink) {
+    const unsigned lane = threadIdx.x & 31;
+    const uint64_t warp = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int locs_per_instr = 32 / lanes_per_loc;
+    const int sub = lane / lanes_per_loc, off = lane % lanes_per_loc;
+    uint64_t acc = 0;
+    for (int it = 0; it < iters; it += 4) {
+        uint64_t v[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint64_t h = mix64(seed ^ mix64(warp * 1000003ULL + (uint64_t)(it + u) * 64 + sub));
+            const uint64_t line = h % n_lines;                       // 256-byte granules
+            v[u] = src[line * 32 + (misalign ? 12 : 0) + off];       // misalign: start 96 B into the granule
+        }
+        acc ^= v[0] ^ v[1] ^ v[2] ^ v[3];
+    }
+    (void)locs_per_instr;
+    if (acc == 0x1234567812345677ULL) *sink = acc;
+}
+
+extern "C" int coala_probe_random_read(uint64_t src_ptr, int64_t bytes, int span_bytes, int misalign, int warps, int iters,
+                                       double* locations_per_s) {
+    if (span_bytes != 8 && span_bytes != 32 && span_bytes != 64 && span_bytes != 128 && span_bytes != 256)
+        COALA_FAIL("probe_random_read: span must be 8, 32, 64, 128 or 256");
+    const int lanes_per_loc = span_bytes / 8;
+    unsigned long long* sink;
+    COALA_CUDA(cudaMalloc(&sink, 8));
+    cudaEvent_t e0, e1;
+    COALA_CUDA(cudaEventCreate(&e0));
+    COALA_CUDA(cudaEventCreate(&e1));
+    const uint64_t n_lines = (uint64_t)bytes / 256 - 2;
+    const int blocks = (warps + 7) / 8;
+    probe_random_kernel<<<blocks, 256>>>(reinterpret_cast<const uint64_t*>(src_ptr), n_lines, lanes_per_loc, 4, 1, misalign, sink);
+    COALA_CUDA(cudaEventRecord(e0));
+    probe_random_kernel<<<blocks, 256>>>(reinterpret_cast<const uint64_t*>(src_ptr), n_lines, lanes_per_loc, iters, 7, misalign, sink);
+    COALA_CUDA(cudaEventRecord(e1));
+    COALA_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    COALA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    *locations_per_s = (double)blocks * 8 * (32 / lanes_per_loc) * iters / (ms * 1e-3);
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
+    return 0;
+}

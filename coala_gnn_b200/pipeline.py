@@ -44,7 +44,8 @@ class BatchEngine(object):
         self.g, self.mgr, self.device = graph, manager, device
         self.seed, self.rank = sampler.seed, sampler.rank
         self.fanouts = list(sampler.fanouts)
-        self.s_sample = torch.cuda.Stream(device=device)
+        # sampling kernels are small and latency bound: high priority so that they take SM slots as gather CTAs retire
+        self.s_sample = torch.cuda.Stream(device=device, priority=-1)
         self.s_gather = torch.cuda.Stream(device=device)
         self.ev_consumed = torch.cuda.Event()
         self.slots = [_Slot(k, self.fanouts, batch_size, manager._out[k], device) for k in range(2)]
@@ -52,6 +53,7 @@ class BatchEngine(object):
             s.sampler._ensure(graph, batch_size)
         self.record = record_gather_events
         self.gather_times = []  # (start, end) event pairs of finished launches
+        self.sample_times = []  # same for distribution + sampling (the other stream)
         self.launched = 0
 
     def consumer_checkpoint(self):
@@ -65,8 +67,14 @@ class BatchEngine(object):
         if slot.used:
             ss.wait_event(slot.ev_gathered)  # the previous gather of this slot read the sampler's id list
         with torch.cuda.stream(ss):
+            if self.record:
+                s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                s0.record(ss)
             seeds = seed_fn(slot, ss)
             slot.sampler.sample_async(self.g, seeds, batch_key(self.seed, t, self.rank), ss.cuda_stream)
+            if self.record:
+                s1.record(ss)
+                self.sample_times.append((s0, s1))
             slot.ev_sampled.record(ss)
         sg.wait_event(slot.ev_sampled)
         sg.wait_event(self.ev_consumed)      # the rows of batch t-2 (same buffer) are no longer needed
@@ -99,6 +107,10 @@ class BatchEngine(object):
         torch.cuda.synchronize()
         return [a.elapsed_time(b) for a, b in self.gather_times]
 
+    def sample_ms(self):
+        torch.cuda.synchronize()
+        return [a.elapsed_time(b) for a, b in self.sample_times]
+
 
 class DevicePipeline(object):
     """Device-resident form of the path for one cache domain: every rank of the domain runs the
@@ -107,7 +119,7 @@ class DevicePipeline(object):
     `refresh_counter` batches and stays on the device.  step() returns the rows of batch t (valid on
     the current stream) while batch t+1 is already in flight."""
 
-    def __init__(self, loader, record_gather_events=False, prefetch=True):
+    def __init__(self, loader, record_gather_events=False, prefetch=True, seed=None):
         self.loader = loader
         self.nd = loader.node_distributor
         self.comm = self.nd.comm_manager
@@ -119,6 +131,8 @@ class DevicePipeline(object):
             raise NotImplementedError("DevicePipeline drives one cache domain; use the drop-in loader for D > 1")
         self.B, self.L = self.nd.batch_size, self.comm.local_size
         self.engine = BatchEngine(self.g, loader.sampler, self.mgr, self.B, self.device, record_gather_events)
+        if seed is not None:
+            self.engine.seed = int(seed)
         self.domain_seeds = [torch.zeros(self.B * self.L, dtype=torch.int64, device=self.device) for _ in range(2)]
         self.meta = torch.zeros(self.nd.meta_len, dtype=torch.int32, device=self.device)
         self.step_idx = 0

@@ -193,6 +193,11 @@ int coala_synth_check_rows(uint64_t rows_ptr, uint64_t idx_ptr, int64_t n, int d
 /* streaming-read bandwidth probe of a device-visible range (host link / peer link / HBM peaks) */
 int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int iters, double* gb_per_s);
 
+/* random-read probe: independent locations per second when each location is read as `span_bytes`
+ * (8/32/64/128/256) contiguous bytes by neighbouring lanes; misalign != 0 starts 96 B into a 256-B granule */
+int coala_probe_random_read(uint64_t src_ptr, int64_t bytes, int span_bytes, int misalign, int warps, int iters,
+                            double* locations_per_s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,70 +1,185 @@
-"""Micro-benchmark of the gather kernel alone (all-miss, all-hit, mixed) + link probes."""
+"""Micro-benchmark of the gather kernel alone, per regime, in one process:
+
+    python scripts/bench_gather.py [--nodes N] [--cache_mb MB] [--dim D] [--gpus 1|2] [--rows R]
+
+  iso_cold / iso_hit      isolated cache on GPU 0: all-miss (host link) and all-hit (HBM)
+  part1_hit               partitioned, 2 shards emulated on GPU 0 (system-scope code path, local HBM)
+  p2p_hit_one / _both     --gpus 2: shards on GPU 0 and GPU 1 mapped into each other; GPU 0 gathers
+                          alone, then both gather at once (half of the rows cross NVLink)
+  p2p_remote_only         ids owned by the peer only: every row crosses NVLink
+Every output row is verified bitwise against the procedural feature hash.  L2 is flushed between
+timed launches.  Prints one JSON dict."""
+import argparse
 import ctypes as C
 import json
+import os
 import sys
-import time
 
 import numpy as np
 import torch
 
-sys.path.insert(0, ".")
-from coala_gnn_b200._lib import lib, check
-from coala_gnn_b200.pybind import Isolated_Cache, Node_distributor_pybind, SSD_GNN_SSD_Controllers
-from coala_gnn_b200 import synth
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from coala_gnn_b200._lib import lib, check  # noqa: E402
+from coala_gnn_b200.pybind import Isolated_Cache, SSD_GNN_NVSHMEM_Cache, NVSHMEM_Manager, Node_distributor_pybind, SSD_GNN_SSD_Controllers  # noqa: E402
+from coala_gnn_b200 import synth  # noqa: E402
 
-N = int(sys.argv[1]) if len(sys.argv) > 1 else 1_000_000
-DIM = 1024
-CACHE_MB = int(sys.argv[2]) if len(sys.argv) > 2 else 4096
-n_rows = 36864
+ap = argparse.ArgumentParser()
+ap.add_argument("--nodes", type=int, default=1_000_000)
+ap.add_argument("--cache_mb", type=int, default=4096)
+ap.add_argument("--dim", type=int, default=1024)
+ap.add_argument("--gpus", type=int, default=1)
+ap.add_argument("--rows", type=int, default=25000)
+ap.add_argument("--iters", type=int, default=6)
+args = ap.parse_args()
+N, DIM, R = args.nodes, args.dim, args.rows
 L = lib()
-t0 = time.time()
-host = torch.empty((N, DIM), dtype=torch.float32).pin_memory()
-print("pinned alloc %.1fs" % (time.time() - t0))
-t0 = time.time()
-check(L.coala_synth_fill_features(host.data_ptr(), 12, 0, N, DIM, DIM, None))
+CD = L.coala_cache_dim_for(DIM)
+RB = CD * 4
+SEED = 12
+res = {"config": vars(args)}
+
+torch.cuda.set_device(0)
+host = torch.empty((N, CD), dtype=torch.float32).pin_memory()
+check(L.coala_synth_fill_features(host.data_ptr(), SEED, 0, N, DIM, CD, None))
 torch.cuda.synchronize()
-print("gpu fill %.2fs" % (time.time() - t0))
 color, topk, score = synth.random_color_meta(N, 5000, 10, seed=1)
 items = np.arange(64, dtype=np.int64)
-nd = Node_distributor_pybind.from_arrays(items.ctypes.data, 0, 8, 1, 1, color, topk, score, device=0)
-ctrl = SSD_GNN_SSD_Controllers(1, 4096, 1024, 0, 0, DIM, True)
-cache = Isolated_Cache(ctrl, nd, 0, 1, CACHE_MB, host.data_ptr())
-res = {}
 gb = C.c_double()
-check(L.coala_probe_read_bandwidth(host.data_ptr(), min(N * DIM * 4, 2 << 30), 3, C.byref(gb)))
+check(L.coala_probe_read_bandwidth(host.data_ptr(), min(N * RB, 2 << 30), 3, C.byref(gb)))
 res["host_link_read_GBs"] = gb.value
-dev = torch.empty(1 << 30, dtype=torch.uint8, device="cuda")
-check(L.coala_probe_read_bandwidth(dev.data_ptr(), 1 << 30, 5, C.byref(gb)))
-res["hbm_read_GBs"] = gb.value
+
+
+def per_device(d):
+    torch.cuda.set_device(d)
+    nd = Node_distributor_pybind.from_arrays(items.ctypes.data, 0, 8, 1, 1, color, topk, score, device=d)
+    ctrl = SSD_GNN_SSD_Controllers(1, RB, 1024, 0, d, DIM, True)
+    out = torch.empty((R, DIM), dtype=torch.float32, device="cuda:%d" % d)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:%d" % d)
+    return dict(nd=nd, ctrl=ctrl, out=out, flush=flush, dev=d)
+
+
+def verify(D, idx_t, n):
+    torch.cuda.set_device(D["dev"])
+    bad = C.c_int64()
+    check(L.coala_synth_check_rows(D["out"].data_ptr(), idx_t.data_ptr(), n, DIM, DIM, SEED, C.byref(bad)))
+    assert bad.value == 0, "%d corrupt rows" % bad.value
+
+
+def timed(label, jobs, batches_per_job, iters=None):
+    """jobs: list of (D, cache); batches_per_job: list (per job) of lists of id arrays. Launches all jobs
+    back to back per iteration (they run concurrently on different GPUs)."""
+    iters = iters or len(batches_per_job[0])
+    ts = [[] for _ in jobs]
+    for it in range(iters):
+        tens, evs = [], []
+        for (D, cache), bl in zip(jobs, batches_per_job):
+            torch.cuda.set_device(D["dev"])
+            tens.append(torch.from_numpy(bl[it % len(bl)]).to("cuda:%d" % D["dev"]))
+            # evict L2 with a READ sweep (a write sweep would leave 126 MB of dirty lines whose write-back
+            # then competes with the timed kernel)
+            check(L.coala_probe_read_bandwidth(D["flush"].data_ptr(), D["flush"].numel(), 1, C.byref(gb)))
+        for j, (D, cache) in enumerate(jobs):
+            torch.cuda.synchronize(D["dev"])
+        for j, (D, cache) in enumerate(jobs):
+            torch.cuda.set_device(D["dev"])
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            st = torch.cuda.current_stream().cuda_stream
+            e0.record()
+            cache.read_feature_async(D["out"].data_ptr(), tens[j].data_ptr(), tens[j].numel(), 0, st)
+            e1.record()
+            evs.append((e0, e1))
+        for j, (D, cache) in enumerate(jobs):
+            torch.cuda.synchronize(D["dev"])
+            ts[j].append(evs[j][0].elapsed_time(evs[j][1]))
+            verify(D, tens[j], tens[j].numel())
+    out = {}
+    for j, (D, cache) in enumerate(jobs):
+        ms = float(np.median(ts[j]))
+        n = len(batches_per_job[j][0])
+        out["gpu%d" % D["dev"]] = dict(ms=ms, min_ms=float(np.min(ts[j])), rows=n, out_GBs=n * RB / ms / 1e6, hbm_alg_GBs=2 * n * RB / ms / 1e6,
+                                       stats=cache.stats(reset=True))
+    res[label] = out
+    print(label, json.dumps(out), flush=True)
+
+
 rng = np.random.default_rng(0)
-out = torch.empty((n_rows, DIM), dtype=torch.float32, device="cuda")
-flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
-
-
-def timed(idx_list, label):
-    ts = []
-    for idx in idx_list:
-        t = torch.from_numpy(idx).cuda()
-        flush.zero_()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        cache.read_feature_async(out.data_ptr(), t.data_ptr(), len(idx), 0, torch.cuda.current_stream().cuda_stream)
-        e1.record()
-        torch.cuda.synchronize()
-        ts.append(e0.elapsed_time(e1))
-        bad = C.c_int64()
-        check(L.coala_synth_check_rows(out.data_ptr(), t.data_ptr(), len(idx), DIM, DIM, 12, C.byref(bad)))
-        assert bad.value == 0, bad.value
-    ms = float(np.median(ts))
-    res[label] = dict(ms=ms, out_GBs=n_rows * 4096 / ms / 1e6, stats=cache.stats(reset=True))
-    print(label, res[label])
-
-
 perm = rng.permutation(N)
-batches = [perm[i * n_rows:(i + 1) * n_rows].astype(np.int64) for i in range(8)]
-timed(batches, "cold_all_miss")
-timed(batches, "warm_all_hit")
-timed(batches[::-1], "warm_all_hit_2")
-mixed = [np.concatenate([b[:n_rows // 2], perm[(10 + i) * n_rows:(10 + i) * n_rows + n_rows // 2]]).astype(np.int64) for i, b in enumerate(batches)]
-timed(mixed, "half_miss")
+nb = min(8, (N * 6 // 10) // R)
+batches = [np.ascontiguousarray(perm[i * R:(i + 1) * R]).astype(np.int64) for i in range(nb)]
+cold_pool = perm[N * 6 // 10:]  # never warmed: every use of one of these ids is a miss
+cold_used = [0]
+
+
+def mixed(frac, parity=None):
+    """one batch per timed iteration: warmed ids with `frac` of them replaced by never-seen ids"""
+    out = []
+    k = int(R * frac)
+    for i in range(args.iters):
+        b = batches[i % nb].copy()
+        pool = cold_pool if parity is None else cold_pool[cold_pool % 2 == parity]
+        c = pool[cold_used[0]:cold_used[0] + k]
+        cold_used[0] += k
+        pos = rng.choice(R, size=len(c), replace=False)
+        b[pos] = c
+        out.append(b)
+    return out
+
+D0 = per_device(0)
+# ---- isolated
+iso = Isolated_Cache(D0["ctrl"], D0["nd"], 0, 1, args.cache_mb, host.data_ptr())
+timed("iso_cold", [(D0, iso)], [batches], iters=nb)
+timed("iso_hit", [(D0, iso)], [batches], iters=args.iters)
+for f in (0.01, 0.03, 0.10):
+    timed("iso_miss%02d" % int(f * 100), [(D0, iso)], [mixed(f)], iters=args.iters)
+del iso
+torch.cuda.empty_cache()
+
+# ---- partitioned, 2 shards emulated on GPU 0 (SYS code path on local memory)
+emu = []
+for g in range(2):
+    NVSHMEM_Manager.current_rank = g
+    emu.append(SSD_GNN_NVSHMEM_Cache(D0["ctrl"], D0["nd"], g, 2, args.cache_mb // 2, host.data_ptr()))
+NVSHMEM_Manager.current_rank = None
+emu[0].attach_local(1, emu[1])
+emu[1].attach_local(0, emu[0])
+timed("part1_cold", [(D0, emu[0])], [batches], iters=nb)
+timed("part1_hit", [(D0, emu[0])], [batches], iters=args.iters)
+for f in (0.01, 0.03, 0.10):
+    timed("part1_miss%02d" % int(f * 100), [(D0, emu[0])], [mixed(f)], iters=args.iters)
+del emu
+torch.cuda.empty_cache()
+
+if args.gpus >= 2:
+    D1 = per_device(1)
+    caches = []
+    for g, D in enumerate((D0, D1)):
+        torch.cuda.set_device(g)
+        NVSHMEM_Manager.current_rank = g
+        caches.append(SSD_GNN_NVSHMEM_Cache(D["ctrl"], D["nd"], g, 2, args.cache_mb, host.data_ptr()))
+    NVSHMEM_Manager.current_rank = None
+    caches[0].attach_local(1, caches[1])
+    caches[1].attach_local(0, caches[0])
+    b1 = batches[::-1]
+    timed("p2p_cold_one", [(D0, caches[0])], [batches], iters=nb)
+    timed("p2p_hit_one", [(D0, caches[0])], [batches], iters=args.iters)
+    timed("p2p_hit_both", [(D0, caches[0]), (D1, caches[1])], [batches, b1], iters=args.iters)
+    for f in (0.01, 0.03, 0.10):
+        timed("p2p_miss%02d_both" % int(f * 100), [(D0, caches[0]), (D1, caches[1])], [mixed(f), mixed(f)], iters=args.iters)
+    odd = [np.ascontiguousarray(perm[perm % 2 == 1][i * R:(i + 1) * R]).astype(np.int64) for i in range(min(4, (N // 2) // R))]
+    even = [np.ascontiguousarray(perm[perm % 2 == 0][i * R:(i + 1) * R]).astype(np.int64) for i in range(min(4, (N // 2) // R))]
+    timed("p2p_remote_only_warm", [(D0, caches[0])], [odd], iters=len(odd))
+    timed("p2p_remote_only_one", [(D0, caches[0])], [odd], iters=args.iters)
+    timed("p2p_local_only_warm", [(D0, caches[0])], [even], iters=len(even))
+    timed("p2p_local_only_one", [(D0, caches[0])], [even], iters=args.iters)
+    timed("p2p_remote_only_both", [(D0, caches[0]), (D1, caches[1])], [odd, even], iters=args.iters)
+    # peer-link streaming-read probe: GPU 0 reads GPU 1's memory
+    torch.cuda.set_device(1)
+    peer_buf = torch.empty(1 << 30, dtype=torch.uint8, device="cuda:1")
+    torch.cuda.set_device(0)
+    check(L.coala_probe_read_bandwidth(peer_buf.data_ptr(), 1 << 30, 5, C.byref(gb)))
+    res["nvlink_read_GBs"] = gb.value
+torch.cuda.set_device(0)
+devbuf = torch.empty(1 << 30, dtype=torch.uint8, device="cuda:0")
+check(L.coala_probe_read_bandwidth(devbuf.data_ptr(), 1 << 30, 5, C.byref(gb)))
+res["hbm_read_GBs"] = gb.value
 print(json.dumps(res))
