@@ -45,6 +45,8 @@ def parse_args():
     p.add_argument("--prewarm_seconds", type=float, default=25.0)
     p.add_argument("--cpu_baseline_seconds", type=float, default=12.0)
     p.add_argument("--no_cpu_baseline", action="store_true")
+    p.add_argument("--hbm_indptr", action="store_true", help="B200 option: sampler keeps a copy of indptr (80 MB) in HBM")
+    p.add_argument("--no_prefetch", action="store_true", help="diagnostic: sample and gather of a batch back to back, no batch in flight")
     p.add_argument("--profile_e2e", action="store_true", help="cProfile the host side of the e2e loop (rank 0) to stderr")
     p.add_argument("--cuda_profiler_range", action="store_true",
                    help="bracket the timed region with cudaProfilerStart/Stop (for `ncu --profile-from-start off`)")
@@ -129,7 +131,7 @@ def build_world(args):
     fan = [int(f) for f in args.fan_out.split(",")]
     train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=0))
     nd = Node_Distributor(comm, train, args.batch_size, ds.color_file, ds.topk_file, ds.score_file, parsing_method=args.distribution)
-    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank)
+    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank, hbm_indptr=args.hbm_indptr)
     backend = args.cache_backend
     loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, sampler, args.batch_size, ds.dim, fan,
                                   args.cache_size, device, refresh_counter=args.refresh_counter, cache_backend=backend,
@@ -182,7 +184,7 @@ def run_ours(args):
     check(lib().coala_probe_read_bandwidth(ds.feat_data.data_ptr(), min(ds.num_nodes * R, 4 << 30), 2, C.byref(gb)))
     host_peak = gb.value
 
-    pipe = DevicePipeline(loader, record_gather_events=True, seed=1001)  # its own sample stream: the e2e leg must not replay these batches
+    pipe = DevicePipeline(loader, record_gather_events=True, seed=1001, prefetch=not args.no_prefetch)  # its own sample stream: the e2e leg must not replay these batches
     spe = pipe.steps_per_epoch()
 
     def pipe_steps(n):
@@ -226,8 +228,41 @@ def run_ours(args):
     h, m, b = cache.stats(reset=True)
     gather_ms = float(np.mean(pipe.gather_ms()))
     sample_ms = float(np.mean(pipe.engine.sample_ms()))
+    if os.environ.get("COALA_SAMPLER_TRACE") and comm.global_rank == 0:
+        sys.stderr.write("sampler trace (ms between ops): %s\n" % ["%.4f" % x for x in pipe.engine.slots[0].sampler.trace()])
     rows = (h + m + b) / args.steps
     value = N * args.steps / (dev_ms * 1e-3)
+
+    # ---- replay: id lists of a few more batches, sampled now and gathered afterwards one by one with nothing
+    # else running on this GPU and the ranks aligned by a barrier: the gather kernel alone, in the
+    # multi-process mapping, on real id lists (each list used once, so L2 holds none of its rows)
+    from coala_gnn_b200.pybind import tensor_from_ptr
+    torch.cuda.synchronize()
+    lists = []
+    for _ in range(8):
+        pipe.step()
+        torch.cuda.synchronize()
+        sl = pipe.engine.slot_of(pipe.step_idx - 1)
+        cnts = (C.c_int64 * (2 * len(fan) + 1))()
+        check(lib().coala_sampler_counts(sl.sampler._h, cnts))
+        idx_ptr, _ = sl.sampler.input_nodes_dev_ptrs()
+        lists.append(tensor_from_ptr(idx_ptr, (int(cnts[0]),), torch.int64, device).clone())
+    for _ in range(3):
+        pipe.step()  # the sampled rows of the lists above are resident now; drain the prefetch
+    torch.cuda.synchronize()
+    cache.stats(reset=True)
+    replay, out_buf = [], pipe.engine.slots[0].out
+    for ids in lists:
+        barrier_sync(comm)
+        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        r0.record()
+        cache.read_feature_async(out_buf.data_ptr(), ids.data_ptr(), ids.numel(), 0, torch.cuda.current_stream().cuda_stream)
+        r1.record()
+        torch.cuda.synchronize()
+        replay.append(r0.elapsed_time(r1))
+    replay_ms = float(np.median(replay))
+    n_last = int(np.mean([x.numel() for x in lists]))
+    rh, rm, rb = cache.stats(reset=True)
 
     # ---- e2e: the drop-in iterator (host seed list, host colour metadata, per-step D2H of the result ids)
     it = iter(loader)
@@ -286,9 +321,11 @@ def run_ours(args):
             "config": {"workload": "%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), SAGE fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
                        % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, B, args.cache_size, args.cache_backend, comm.num_master_process, L, args.distribution),
                        "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (> 126 MB L2, no reuse between steps)" % (rows * R / 1e6),
-                       "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter},
+                       "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter,
+                       "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr copy in HBM" if args.hbm_indptr else "")},
             "hit_ratio": hs / max(1.0, hs + ms_ + bs), "rows_per_step": rows,
             "gather_GBs": rows * R / t_meas / 1e9, "sample_stream_ms": sample_ms,
+            "gather_replay": {"ms": replay_ms, "rows": n_last, "out_GBs": n_last * R / replay_ms / 1e6, "hit_ratio": rh / max(1, rh + rm + rb)},
             "roofline": {"bound": "hbm", "achieved": alg_hbm / t_meas / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": alg_hbm / t_meas / 1e9 / hbm_peak,
                          "traffic": None, "peak_source": peak_src, "kernel": "coala_gather_kernel", "kernel_ms": gather_ms,
                          "kernel_share_of_step": gather_ms / (dev_ms / args.steps),

@@ -40,6 +40,9 @@ SIGNATURES = {
     "coala_cache_ipc_handle": (_i32, [_vp, _vp]),
     "coala_cache_attach_ipc": (_i32, [_vp, _i32, _vp]),
     "coala_cache_attach_local": (_i32, [_vp, _i32, _vp]),
+    "coala_cache_is_fd_shared": (_i32, [_vp]),
+    "coala_cache_export_fd": (_i32, [_vp]),
+    "coala_cache_attach_fd": (_i32, [_vp, _i32, _i32]),
     "coala_cache_read_feature": (_i32, [_vp, _u64, _u64, _i64]),
     "coala_cache_read_feature_async": (_i32, [_vp, _u64, _u64, _i64, _u64, _vp]),
     "coala_cache_read_feature_serial": (_i32, [_vp, _u64, _u64, _i64]),
@@ -56,6 +59,8 @@ SIGNATURES = {
     "coala_sampler_create": (_vp, [_i32, _u64, _u64, _u64, _i64, _i32, _vp, _i32]),
     "coala_sampler_destroy": (None, [_vp]),
     "coala_sampler_max_sample": (_i64, [_vp]),
+    "coala_sampler_stage_indptr": (_i32, [_vp]),
+    "coala_sampler_trace": (_i32, [_vp, _vp, _i32]),
     "coala_sampler_sample_async": (_i32, [_vp, _u64, _i32, _u64, _vp]),
     "coala_sampler_counts": (_i32, [_vp, _vp]),
     "coala_sampler_layer_ptrs": (_i32, [_vp, _i32, _vp, _vp, _vp, _vp]),

@@ -3,6 +3,8 @@
 // M/isolated_cache.h:519-636 / M/nvshmem_cache.h:524-641.
 #include "cache.cuh"
 #include "distributor.h"
+#include "vmm.h"
+#include <unistd.h>
 #include <vector>
 
 namespace {
@@ -53,6 +55,9 @@ struct coala_cache {
     CacheParams params;
     unsigned long long* d_stats = nullptr;
     void* ipc_mapped[COALA_MAX_GPUS] = {nullptr};
+    bool vmm = false;                    // slab allocated with cuMemCreate (shareable as a POSIX fd)
+    VmmRegion region;                    // own slab when vmm
+    VmmRegion peer_region[COALA_MAX_GPUS];
     int copy_engine = 0;
     int waves = 2;
     int ctas_per_sm = 2;   // residency cap of the gather (see launch_gather)
@@ -93,7 +98,9 @@ static int launch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t
         size_t smem = 0;
         if (c->ctas_per_sm > 0 && c->ctas_per_sm < MINB) {
             resident = c->ctas_per_sm;
-            smem = (size_t)(c->smem_per_sm / resident) - 2048;  // per-CTA reservation incl. the driver's 1 KB
+            // big enough that resident+1 CTAs cannot fit, small enough to leave >= 16 KB per SM for the
+            // (1 KB each) driver reservations of the other stream's CTAs
+            smem = (size_t)(c->smem_per_sm / resident) - 16384;
             // per device, and cheap: set on every launch rather than tracking (device, instantiation) pairs
             COALA_CUDA(cudaFuncSetAttribute(coala_gather_kernel<VPL, SYS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         }
@@ -143,8 +150,18 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     if (c->num_sets == 0) { coala_set_error("coala_cache_create: cache smaller than one set"); delete c; return nullptr; }
     c->num_colors = nd ? coala_nd_num_colors(nd) : 0;
     c->layout = SlabLayout(c->num_sets, c->row_bytes, c->num_colors);
-    cudaError_t e = cudaMalloc(&c->slab, c->layout.total);
-    if (e != cudaSuccess) { coala_set_error(std::string("cudaMalloc(cache slab) failed: ") + cudaGetErrorString(e)); delete c; return nullptr; }
+    // a shard that peers will map is allocated through the VMM API (2 MB-granular mappings on every
+    // importer; see vmm.h for the measurement behind this); COALA_CACHE_LEGACY_IPC=1 keeps cudaMalloc + CUDA IPC
+    const char* legacy = getenv("COALA_CACHE_LEGACY_IPC");
+    c->vmm = kind == COALA_CACHE_PARTITIONED && n_gpus > 1 && !(legacy && atoi(legacy));
+    if (c->vmm) {
+        std::string err = vmm_alloc(&c->region, c->layout.total, device);
+        if (!err.empty()) { coala_set_error("cache slab: " + err); delete c; return nullptr; }
+        c->slab = reinterpret_cast<uint8_t*>(c->region.va);
+    } else {
+        cudaError_t e = cudaMalloc(&c->slab, c->layout.total);
+        if (e != cudaSuccess) { coala_set_error(std::string("cudaMalloc(cache slab) failed: ") + cudaGetErrorString(e)); delete c; return nullptr; }
+    }
     ShardView own = c->layout.view(c->slab);
     // tags: empty = id field all ones, version 0 (reference keys_ are memset 0xFF, M/isolated_cache.h:546)
     {
@@ -201,7 +218,10 @@ extern "C" void coala_cache_destroy(coala_cache* c) {
     cudaDeviceSynchronize();
     for (int g = 0; g < COALA_MAX_GPUS; g++)
         if (c->ipc_mapped[g]) cudaIpcCloseMemHandle(c->ipc_mapped[g]);
-    if (c->slab) cudaFree(c->slab);
+    for (int g = 0; g < COALA_MAX_GPUS; g++)
+        if (c->peer_region[g].handle) vmm_free(&c->peer_region[g]);
+    if (c->vmm) vmm_free(&c->region);
+    else if (c->slab) cudaFree(c->slab);
     if (c->d_stats) cudaFree(c->d_stats);
     delete c;
 }
@@ -215,6 +235,7 @@ extern "C" uint64_t coala_cache_color_counters_dev_ptr(coala_cache* c) {
 extern "C" int coala_cache_ipc_handle(coala_cache* c, void* handle64) {
     static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
     COALA_CUDA(cudaSetDevice(c->device));
+    if (c->vmm) COALA_FAIL("ipc_handle: this shard is shared as a file descriptor (coala_cache_export_fd)");
     cudaIpcMemHandle_t h;
     COALA_CUDA(cudaIpcGetMemHandle(&h, c->slab));
     memcpy(handle64, &h, 64);
@@ -245,8 +266,35 @@ extern "C" int coala_cache_attach_ipc(coala_cache* c, int peer, const void* hand
     return attach_base(c, peer, static_cast<uint8_t*>(base));
 }
 
+extern "C" int coala_cache_is_fd_shared(coala_cache* c) { return c->vmm ? 1 : 0; }
+
+extern "C" int coala_cache_export_fd(coala_cache* c) {
+    if (!c->vmm) { coala_set_error("export_fd: shard was not allocated with the VMM API"); return -1; }
+    std::string err;
+    int fd = vmm_export_fd(c->region, &err);
+    if (fd < 0) coala_set_error(err);
+    return fd;
+}
+
+extern "C" int coala_cache_attach_fd(coala_cache* c, int peer, int fd) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    if (peer == c->params.my_slot) return 0;
+    if (peer < 0 || peer >= c->n_gpus) COALA_FAIL("attach_fd: peer rank out of range");
+    if (!c->vmm) COALA_FAIL("attach_fd: this cache uses CUDA IPC handles");
+    std::string err = vmm_import(&c->peer_region[peer], fd, c->region.size, c->device);
+    if (!err.empty()) COALA_FAIL("attach_fd: " + err);
+    return attach_base(c, peer, reinterpret_cast<uint8_t*>(c->peer_region[peer].va));
+}
+
 extern "C" int coala_cache_attach_local(coala_cache* c, int peer, coala_cache* other) {
     COALA_CUDA(cudaSetDevice(c->device));
+    if (other->vmm) {  // same process: one more device on the peer's existing mapping
+        if (other->device != c->device) {
+            std::string err = vmm_grant(other->region, c->device);
+            if (!err.empty()) COALA_FAIL("attach_local: " + err);
+        }
+        return attach_base(c, peer, other->slab);
+    }
     if (other->device != c->device) {
         int can = 0;
         COALA_CUDA(cudaDeviceCanAccessPeer(&can, c->device, other->device));

@@ -68,11 +68,12 @@ __global__ void ht_reset_kernel(HashTable t) {
 // ---- K1: one warp per frontier node: indptr pair, picks, neighbour ids into fixed-stride slots
 __global__ void __launch_bounds__(256) sample_rows_kernel(const int64_t* __restrict__ indptr, const int64_t* __restrict__ indices,
                                                           const int64_t* __restrict__ frontier, const int64_t* __restrict__ n_front,
-                                                          int fanout, uint64_t layer_key, HashTable ht,
+                                                          int fanout, const uint64_t* __restrict__ batch_key, int layer, HashTable ht,
                                                           int64_t* __restrict__ slot_src, int64_t* __restrict__ slot_eid,
                                                           int* __restrict__ cnt) {
     const int lane = threadIdx.x & 31;
     const int64_t ns = *n_front;
+    const uint64_t layer_key = mix64(*batch_key + (uint64_t)(layer + 1) * LAYER_MUL);
     const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
     for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; i < ns; i += nwarps) {
         const int64_t v = frontier[i];
@@ -81,11 +82,21 @@ __global__ void __launch_bounds__(256) sample_rows_kernel(const int64_t* __restr
         const int64_t start = __shfl_sync(0xffffffffu, p, 0);
         const int64_t deg = __shfl_sync(0xffffffffu, p, 1) - start;
         if (lane == 0) ht_insert_min(ht, v, (int)i);  // dst nodes take local ids 0..ns-1
-        int64_t mypos = -1;
+        // The host link serves ~154 M independent requests/s whatever their size up to 256 B (measured,
+        // scripts/probe_links.py), so a row is fetched as ONE coalesced span (<= 64 neighbours: two
+        // 256-B requests at most) issued before the picks are computed, instead of one request per pick.
+        constexpr int ROW_SPAN = 64;
+        const bool whole_row = deg <= ROW_SPAN;
+        int64_t r0 = 0, r1 = 0;
+        if (whole_row) {
+            if (lane < deg) r0 = indices[start + lane];
+            if (lane + 32 < deg) r1 = indices[start + 32 + lane];
+        }
+        int64_t mypos = -1, myval = 0;
         int k;
         if (deg <= fanout) {
             k = (int)deg;
-            if (lane < k) mypos = lane;
+            if (lane < k) { mypos = lane; myval = r0; }  // fanout <= 32 < ROW_SPAN: the row is in r0
         } else {
             k = fanout;
             // partial Fisher-Yates over the virtual array a[x] = x; the sparse swap map lives one
@@ -125,29 +136,48 @@ __global__ void __launch_bounds__(256) sample_rows_kernel(const int64_t* __restr
                 if (ru == lane) sorted = pu;
             }
             if (lane < k) mypos = sorted;
+            if (whole_row) {  // pick the neighbour ids out of the registers that hold the row
+                for (int u = 0; u < k; u++) {
+                    const int pu = (int)__shfl_sync(0xffffffffu, sorted, u);
+                    const int64_t a = __shfl_sync(0xffffffffu, r0, pu & 31);
+                    const int64_t b = __shfl_sync(0xffffffffu, r1, pu & 31);
+                    if (lane == u) myval = pu < 32 ? a : b;
+                }
+            } else if (lane < k) {
+                myval = indices[start + mypos];
+            }
         }
         if (lane < k) {
-            const int64_t e = start + mypos;
-            slot_src[i * fanout + lane] = indices[e];
-            slot_eid[i * fanout + lane] = e;  // CSC position; the edge id is looked up on demand (coala_sampler_edge_ids)
+            slot_src[i * fanout + lane] = myval;
+            slot_eid[i * fanout + lane] = start + mypos;  // CSC position; the edge id is looked up on demand (coala_lookup_edge_ids)
         }
         if (lane == 0) cnt[i] = k;
     }
 }
 
 // ---- single-CTA exclusive scan of int32.  Thread t owns the contiguous chunk [t*per, (t+1)*per):
-// two sweeps over L2-resident data around one block-level scan of the 1024 chunk sums (frontier /
-// edge counts are <= ~1e6 here, so per stays small and no inter-block carry is needed).
-__global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ in, int* __restrict__ out, const int64_t* __restrict__ n_ptr,
-                                                    int64_t mul, int64_t* __restrict__ total_out, const int64_t* __restrict__ add_ptr,
-                                                    int64_t* __restrict__ total_plus_out) {
-    __shared__ int warp_sum[32];
+// two sweeps over L2-resident data around one block-level scan of the chunk sums (frontier / edge
+// counts are <= ~1e6 here, so per stays small and no inter-block carry is needed).  512 threads x
+// 32 registers on purpose: the CTA must fit next to the resident gather CTAs of the previous batch
+// (a 1024-thread CTA cannot, and would wait for a gather CTA to retire — four times per batch).
+constexpr int SCAN_T = 512;
+__global__ void __launch_bounds__(SCAN_T) scan_kernel(const int* __restrict__ in, int* __restrict__ out, const int64_t* __restrict__ n_ptr,
+                                                      int64_t mul, int64_t* __restrict__ total_out, const int64_t* __restrict__ add_ptr,
+                                                      int64_t* __restrict__ total_plus_out) {
+    __shared__ int warp_sum[SCAN_T / 32];
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int64_t n = *n_ptr * mul;
-    const int64_t per = (n + 1023) >> 10;
+    const int64_t per = (((n + SCAN_T - 1) / SCAN_T) + 3) & ~(int64_t)3;  // multiple of 4: chunks start 16-B aligned
     const int64_t lo = min(n, (int64_t)tid * per), hi = min(n, lo + per);
     int sum = 0;
-    for (int64_t i = lo; i < hi; i++) sum += in[i];
+    {
+        int64_t i = lo;
+        for (; i + 4 <= hi; i += 4) {
+            const int4 x = *reinterpret_cast<const int4*>(in + i);
+            sum += x.x + x.y + x.z + x.w;
+        }
+        for (; i < hi; i++) sum += in[i];
+    }
     int incl = sum;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -157,28 +187,40 @@ __global__ void __launch_bounds__(1024) scan_kernel(const int* __restrict__ in, 
     if (lane == 31) warp_sum[w] = incl;
     __syncthreads();
     if (w == 0) {
-        int sw = warp_sum[lane], si = sw;
+        int sw = lane < SCAN_T / 32 ? warp_sum[lane] : 0, si = sw;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             int y = __shfl_up_sync(0xffffffffu, si, d);
             if (lane >= d) si += y;
         }
-        warp_sum[lane] = si - sw;  // exclusive warp offsets
+        if (lane < SCAN_T / 32) warp_sum[lane] = si - sw;  // exclusive warp offsets
     }
     __syncthreads();
     int run = warp_sum[w] + incl - sum;  // exclusive prefix of this thread's chunk
-    for (int64_t i = lo; i < hi; i++) {
-        const int x = in[i];
-        out[i] = run;
-        run += x;
+    {
+        int64_t i = lo;
+        for (; i + 4 <= hi; i += 4) {
+            const int4 x = *reinterpret_cast<const int4*>(in + i);
+            int4 o;
+            o.x = run; o.y = run + x.x; o.z = o.y + x.y; o.w = o.z + x.z;
+            run = o.w + x.w;
+            *reinterpret_cast<int4*>(out + i) = o;
+        }
+        for (; i < hi; i++) { const int x = in[i]; out[i] = run; run += x; }
     }
-    if (tid == 1023) {  // run == grand total (chunks past n are empty)
+    if (tid == SCAN_T - 1) {  // run == grand total (chunks past n are empty)
         if (total_out) *total_out = run;
         if (total_plus_out) *total_plus_out = run + *add_ptr;
     }
 }
 
-__global__ void set_count_kernel(int64_t* dst, int64_t v) { *dst = v; }
+// ---- prologue: the only node whose arguments change from batch to batch (seed list, count, RNG key);
+// everything after it reads these from device memory, so the rest of the sample is a fixed CUDA graph
+__global__ void prologue_kernel(const int64_t* __restrict__ seeds, int64_t ns, uint64_t rng_key, int64_t* __restrict__ frontier0,
+                                int64_t* __restrict__ n_front0, uint64_t* __restrict__ key_out) {
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < ns; i += (int64_t)gridDim.x * blockDim.x) frontier0[i] = seeds[i];
+    if (blockIdx.x == 0 && threadIdx.x == 0) { *n_front0 = ns; *key_out = rng_key; }
+}
 
 // ---- K3: compact the fixed-stride slots into the edge list and insert sources (min position)
 __global__ void compact_insert_kernel(const int64_t* __restrict__ slot_src, const int64_t* __restrict__ slot_eid,
@@ -262,7 +304,42 @@ struct coala_sampler {
     int64_t* h_counts = nullptr;       // pinned mirror
     cudaEvent_t done = nullptr;
     int sm_count = 148;
+    int64_t* indptr_hbm = nullptr;     // optional HBM copy of indptr (coala_sampler_stage_indptr)
+    uint64_t* d_key = nullptr;         // RNG key of the batch in flight
+    // the whole sample as one CUDA graph: one launch instead of 16 (every launch is a command fetch over
+    // the same host link the path keeps busy); only the prologue node's arguments are patched per batch
+    bool use_graph = true;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t graph_exec = nullptr;
+    cudaGraphNode_t prologue_node = nullptr;
+    cudaStream_t cap_stream = nullptr;
+    // diagnostics (COALA_SAMPLER_TRACE=1): one event after every enqueued operation of a sample
+    bool trace = false;
+    std::vector<cudaEvent_t> tev;
+    int tev_used = 0;
+    std::vector<double> tsum;
+    int tcount = 0;
 };
+
+static void trace_mark(coala_sampler* s, cudaStream_t st) {
+    if (!s->trace) return;
+    if (s->tev_used == (int)s->tev.size()) { cudaEvent_t e; cudaEventCreate(&e); s->tev.push_back(e); }
+    cudaEventRecord(s->tev[s->tev_used++], st);
+}
+static void trace_collect(coala_sampler* s) {  // fold the previous sample's events into the running sums
+    if (!s->trace || s->tev_used < 2) return;
+    if (cudaEventSynchronize(s->tev[s->tev_used - 1]) != cudaSuccess) return;
+    if ((int)s->tsum.size() < s->tev_used - 1) s->tsum.resize(s->tev_used - 1, 0.0);
+    for (int i = 0; i + 1 < s->tev_used; i++) { float ms = 0; cudaEventElapsedTime(&ms, s->tev[i], s->tev[i + 1]); s->tsum[i] += ms; }
+    s->tcount++;
+    s->tev_used = 0;
+}
+extern "C" int coala_sampler_trace(coala_sampler* s, double* avg_ms, int max_n) {
+    trace_collect(s);
+    int n = (int)s->tsum.size() < max_n ? (int)s->tsum.size() : max_n;
+    for (int i = 0; i < n; i++) avg_ms[i] = s->tcount ? s->tsum[i] / s->tcount : 0.0;
+    return n;
+}
 
 extern "C" coala_sampler* coala_sampler_create(int device, uint64_t indptr_ptr, uint64_t indices_ptr, uint64_t edge_ids_ptr,
                                                int64_t num_nodes, int max_seeds, const int* fanouts, int n_layers) {
@@ -305,6 +382,7 @@ extern "C" coala_sampler* coala_sampler_create(int device, uint64_t indptr_ptr, 
     s->ht.mask = cap - 1;
     COALA_CUDA_NULL(cudaMalloc(&s->ht.keys, cap * 8));
     COALA_CUDA_NULL(cudaMalloc(&s->ht.vals, cap * 4));
+    COALA_CUDA_NULL(cudaMalloc(&s->d_key, 8));
     COALA_CUDA_NULL(cudaMalloc(&s->d_counts, (2 * MAX_LAYERS + 2) * 8));
     COALA_CUDA_NULL(cudaMemset(s->d_counts, 0, (2 * MAX_LAYERS + 2) * 8));
     COALA_CUDA_NULL(cudaHostAlloc(&s->h_counts, (2 * MAX_LAYERS + 2) * 8, cudaHostAllocDefault));
@@ -313,6 +391,9 @@ extern "C" coala_sampler* coala_sampler_create(int device, uint64_t indptr_ptr, 
     cudaDeviceProp prop;
     COALA_CUDA_NULL(cudaGetDeviceProperties(&prop, device));
     s->sm_count = prop.multiProcessorCount;
+    if (const char* e = getenv("COALA_SAMPLER_TRACE")) s->trace = atoi(e) != 0;
+    if (const char* e = getenv("COALA_SAMPLER_GRAPH")) s->use_graph = atoi(e) != 0;
+    if (s->trace) s->use_graph = false;  // per-kernel events only make sense for direct launches
     return s;
 }
 
@@ -323,6 +404,10 @@ extern "C" void coala_sampler_destroy(coala_sampler* s) {
     for (int l = 0; l <= s->L; l++) cudaFree(s->frontier[l]);
     for (int l = 0; l < s->L; l++) { cudaFree(s->e_src[l]); cudaFree(s->e_dst[l]); cudaFree(s->e_id[l]); cudaFree(s->e_src_local[l]); }
     cudaFree(s->slot_src); cudaFree(s->slot_eid); cudaFree(s->cnt); cudaFree(s->off); cudaFree(s->val);
+    cudaFree(s->indptr_hbm); cudaFree(s->d_key);
+    if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
+    if (s->graph) cudaGraphDestroy(s->graph);
+    if (s->cap_stream) cudaStreamDestroy(s->cap_stream);
     cudaFree(s->flag); cudaFree(s->rank); cudaFree(s->ht.keys); cudaFree(s->ht.vals); cudaFree(s->d_counts);
     if (s->h_counts) cudaFreeHost(s->h_counts);
     if (s->done) cudaEventDestroy(s->done);
@@ -330,6 +415,17 @@ extern "C" void coala_sampler_destroy(coala_sampler* s) {
 }
 
 extern "C" int64_t coala_sampler_max_sample(coala_sampler* s) { return s->ns_max[s->L]; }
+
+extern "C" int coala_sampler_stage_indptr(coala_sampler* s) {
+    if (s->indptr_hbm) return 0;
+    COALA_CUDA(cudaSetDevice(s->device));
+    COALA_CUDA(cudaMalloc(&s->indptr_hbm, (size_t)(s->num_nodes + 1) * 8));
+    COALA_CUDA(cudaMemcpy(s->indptr_hbm, s->indptr, (size_t)(s->num_nodes + 1) * 8, cudaMemcpyDefault));
+    s->indptr = s->indptr_hbm;
+    if (s->graph_exec) { cudaGraphExecDestroy(s->graph_exec); s->graph_exec = nullptr; }
+    if (s->graph) { cudaGraphDestroy(s->graph); s->graph = nullptr; }
+    return 0;
+}
 extern "C" uint64_t coala_sampler_input_count_dev_ptr(coala_sampler* s) { return (uint64_t)(s->d_counts + s->L); }
 
 static inline unsigned grid_for(int64_t work, int per_block, int cap) {
@@ -339,39 +435,89 @@ static inline unsigned grid_for(int64_t work, int per_block, int cap) {
     return (unsigned)b;
 }
 
-extern "C" int coala_sampler_sample_async(coala_sampler* s, uint64_t seeds_dev_ptr, int ns, uint64_t rng_key, void* stream) {
-    if (ns < 0 || ns > s->max_seeds) COALA_FAIL("sampler: more seeds than max_seeds");
-    COALA_CUDA(cudaSetDevice(s->device));
-    cudaStream_t st = static_cast<cudaStream_t>(stream);
+// enqueue every operation of one sample on `st` (directly, or while `st` is being captured)
+static int enqueue_sample(coala_sampler* s, const int64_t* seeds, int64_t ns, uint64_t rng_key, cudaStream_t st) {
     const int L = s->L;
     int64_t* d_nf = s->d_counts;          // frontier sizes [0..L]
     int64_t* d_ne = s->d_counts + L + 1;  // edge counts [0..L-1]
-    const int64_t ns64 = ns;
+    trace_mark(s, st);
     // the frontier size of round 0 is the only count the host knows
-    set_count_kernel<<<1, 1, 0, st>>>(d_nf, ns64);
-    COALA_CUDA(cudaMemcpyAsync(s->frontier[0], reinterpret_cast<const void*>(seeds_dev_ptr), (size_t)ns * 8, cudaMemcpyDefault, st));
+    prologue_kernel<<<4, 256, 0, st>>>(seeds, ns, rng_key, s->frontier[0], d_nf, s->d_key);
+    trace_mark(s, st);
     const int cap = s->sm_count * 8;
     for (int l = 0; l < L; l++) {
         const int f = s->fanout[l];
-        const uint64_t lkey = mix64(rng_key + (uint64_t)(l + 1) * LAYER_MUL);
         HashTable ht = s->ht;
         // table sized for this round only: keeps the reset cheap for the small early rounds
         uint64_t need = 1024;
         while (need < 2 * (uint64_t)s->ns_max[l + 1]) need <<= 1;
         ht.mask = need - 1;
         ht_reset_kernel<<<grid_for((int64_t)need, 1024, cap), 256, 0, st>>>(ht);
+        trace_mark(s, st);
         sample_rows_kernel<<<grid_for(s->ns_max[l], 8, cap), 256, 0, st>>>(s->indptr, s->indices, s->frontier[l], d_nf + l, f,
-                                                                          lkey, ht, s->slot_src, s->slot_eid, s->cnt);
-        scan_kernel<<<1, 1024, 0, st>>>(s->cnt, s->off, d_nf + l, 1, d_ne + l, nullptr, nullptr);
+                                                                          s->d_key, l, ht, s->slot_src, s->slot_eid, s->cnt);
+        trace_mark(s, st);
+        scan_kernel<<<1, SCAN_T, 0, st>>>(s->cnt, s->off, d_nf + l, 1, d_ne + l, nullptr, nullptr);
+        trace_mark(s, st);
         compact_insert_kernel<<<grid_for(s->ne_max[l], 256, cap), 256, 0, st>>>(s->slot_src, s->slot_eid, s->cnt, s->off, d_nf + l, f, ht,
                                                                               s->e_src[l], s->e_dst[l], s->e_id[l]);
+        trace_mark(s, st);
         flag_first_kernel<<<grid_for(s->ne_max[l], 256, cap), 256, 0, st>>>(s->e_src[l], d_ne + l, d_nf + l, ht, s->val, s->flag);
-        scan_kernel<<<1, 1024, 0, st>>>(s->flag, s->rank, d_ne + l, 1, nullptr, d_nf + l, d_nf + l + 1);
+        trace_mark(s, st);
+        scan_kernel<<<1, SCAN_T, 0, st>>>(s->flag, s->rank, d_ne + l, 1, nullptr, d_nf + l, d_nf + l + 1);
+        trace_mark(s, st);
         relabel_kernel<<<grid_for(s->ne_max[l], 256, cap), 256, 0, st>>>(s->e_src[l], s->val, s->flag, s->rank, d_ne + l, d_nf + l,
                                                                         s->frontier[l], s->e_src_local[l], s->frontier[l + 1]);
+        trace_mark(s, st);
     }
     COALA_CUDA(cudaGetLastError());
     COALA_CUDA(cudaMemcpyAsync(s->h_counts, s->d_counts, (2 * L + 1) * 8, cudaMemcpyDeviceToHost, st));
+    trace_mark(s, st);
+    return 0;
+}
+
+static int build_graph(coala_sampler* s) {
+    if (!s->cap_stream) COALA_CUDA(cudaStreamCreateWithFlags(&s->cap_stream, cudaStreamNonBlocking));
+    COALA_CUDA(cudaStreamBeginCapture(s->cap_stream, cudaStreamCaptureModeRelaxed));
+    int rc = enqueue_sample(s, s->frontier[0], 0, 0, s->cap_stream);  // placeholder arguments, patched per launch
+    cudaError_t e = cudaStreamEndCapture(s->cap_stream, &s->graph);
+    if (rc) return -1;
+    COALA_CUDA(e);
+    size_t n_root = 1;
+    COALA_CUDA(cudaGraphGetRootNodes(s->graph, &s->prologue_node, &n_root));
+    if (n_root != 1) COALA_FAIL("sampler graph: expected a single root node");
+    cudaGraphNodeType ty;
+    COALA_CUDA(cudaGraphNodeGetType(s->prologue_node, &ty));
+    if (ty != cudaGraphNodeTypeKernel) COALA_FAIL("sampler graph: root node is not the prologue kernel");
+    COALA_CUDA(cudaGraphInstantiate(&s->graph_exec, s->graph, 0));
+    return 0;
+}
+
+extern "C" int coala_sampler_sample_async(coala_sampler* s, uint64_t seeds_dev_ptr, int ns, uint64_t rng_key, void* stream) {
+    if (ns < 0 || ns > s->max_seeds) COALA_FAIL("sampler: more seeds than max_seeds");
+    COALA_CUDA(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t* seeds = reinterpret_cast<const int64_t*>(seeds_dev_ptr);
+    if (!s->use_graph) {
+        trace_collect(s);
+        if (enqueue_sample(s, seeds, ns, rng_key, st)) return -1;
+    } else {
+        if (!s->graph_exec && build_graph(s)) return -1;
+        int64_t ns64 = ns;
+        int64_t* f0 = s->frontier[0];
+        int64_t* nf0 = s->d_counts;
+        uint64_t* key = s->d_key;
+        void* args[6] = {&seeds, &ns64, &rng_key, &f0, &nf0, &key};
+        cudaKernelNodeParams kp;
+        memset(&kp, 0, sizeof(kp));
+        kp.func = reinterpret_cast<void*>(prologue_kernel);
+        kp.gridDim = dim3(4);
+        kp.blockDim = dim3(256);
+        kp.sharedMemBytes = 0;
+        kp.kernelParams = args;
+        COALA_CUDA(cudaGraphExecKernelNodeSetParams(s->graph_exec, s->prologue_node, &kp));
+        COALA_CUDA(cudaGraphLaunch(s->graph_exec, st));
+    }
     COALA_CUDA(cudaEventRecord(s->done, st));
     return 0;
 }

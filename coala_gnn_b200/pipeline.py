@@ -23,9 +23,9 @@ from .sampler import MultiLayerNeighborSampler, batch_key
 
 
 class _Slot(object):
-    def __init__(self, k, fanouts, batch_size, out, device):
+    def __init__(self, k, fanouts, batch_size, out, device, hbm_indptr=None):
         self.k = k
-        self.sampler = MultiLayerNeighborSampler(fanouts)
+        self.sampler = MultiLayerNeighborSampler(fanouts, hbm_indptr=hbm_indptr)
         self.seeds = torch.zeros(batch_size, dtype=torch.int64, device=device)
         self.seeds_pin = torch.zeros(batch_size, dtype=torch.int64).pin_memory()
         self.out = out
@@ -48,7 +48,7 @@ class BatchEngine(object):
         self.s_sample = torch.cuda.Stream(device=device, priority=-1)
         self.s_gather = torch.cuda.Stream(device=device)
         self.ev_consumed = torch.cuda.Event()
-        self.slots = [_Slot(k, self.fanouts, batch_size, manager._out[k], device) for k in range(2)]
+        self.slots = [_Slot(k, self.fanouts, batch_size, manager._out[k], device, getattr(sampler, "hbm_indptr", None)) for k in range(2)]
         for s in self.slots:
             s.sampler._ensure(graph, batch_size)
         self.record = record_gather_events

@@ -276,16 +276,59 @@ class SSD_GNN_NVSHMEM_Cache(_CacheBase):
         check(lib().coala_cache_ipc_handle(self._h, buf), "ipc_handle")
         return buf.raw
 
+    _connect_seq = 0
+
     def connect(self, group):
-        """Collective over the cache domain: exchange one IPC handle per shard and map the peers."""
+        """Collective over the cache domain: every rank maps every peer's shard.  Shards are shared as
+        POSIX file descriptors (VMM allocations) sent over unix sockets; with COALA_CACHE_LEGACY_IPC=1
+        as 64-byte CUDA IPC handles."""
         import torch.distributed as dist
-        handles = [None] * self.num_gpus
-        dist.all_gather_object(handles, self.ipc_handle(), group=group)
         me = dist.get_rank(group)
-        for r, h in enumerate(handles):
+        if not lib().coala_cache_is_fd_shared(self._h):
+            handles = [None] * self.num_gpus
+            dist.all_gather_object(handles, self.ipc_handle(), group=group)
+            for r, h in enumerate(handles):
+                if r != me:
+                    check(lib().coala_cache_attach_ipc(self._h, r, h), "attach_ipc")
+            dist.barrier(group=group)
+            return
+        import os
+        import socket
+        SSD_GNN_NVSHMEM_Cache._connect_seq += 1
+        tag = "%s_%d_%d" % (os.environ.get("MASTER_PORT", "0"), dist.get_global_rank(group, 0), SSD_GNN_NVSHMEM_Cache._connect_seq)
+
+        def name(r):  # abstract unix socket: no file system entry, gone when closed
+            return "\0coala_b200_%s_%d" % (tag, r)
+        my_fd = lib().coala_cache_export_fd(self._h)
+        if my_fd < 0:
+            raise CoalaError("export_fd: " + lib().coala_last_error().decode())
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(name(me))
+        srv.listen(self.num_gpus)
+        dist.barrier(group=group)  # every rank is listening
+        conns = {}
+        for r in range(self.num_gpus):
             if r != me:
-                check(lib().coala_cache_attach_ipc(self._h, r, h), "attach_ipc")
-        dist.barrier(group=group)
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.connect(name(r))  # completes from the listen backlog, no accept needed yet
+                c.sendall(bytes([me]))
+                conns[r] = c
+        served = []
+        for _ in range(self.num_gpus - 1):
+            c, _addr = srv.accept()
+            c.recv(1)
+            socket.send_fds(c, [b"f"], [my_fd])
+            served.append(c)
+        for r, c in conns.items():
+            _msg, fds, _flags, _addr = socket.recv_fds(c, 1, 1)
+            try:
+                check(lib().coala_cache_attach_fd(self._h, r, fds[0]), "attach_fd")
+            finally:
+                os.close(fds[0])
+        dist.barrier(group=group)  # every rank has imported every shard
+        for c in list(conns.values()) + served + [srv]:
+            c.close()
+        os.close(my_fd)
 
     def attach_local(self, peer_rank, peer_cache):
         self._peers.append(peer_cache)

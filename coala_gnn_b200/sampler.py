@@ -131,7 +131,9 @@ class MultiLayerNeighborSampler:
     """Uniform in-neighbour sampling without replacement, one round per fan-out in reverse order,
     each followed by to_block. `seed` fixes the RNG stream; the k-th call uses batch_key(seed, k, rank)."""
 
-    def __init__(self, fanouts, seed=0, rank=0):
+    def __init__(self, fanouts, seed=0, rank=0, hbm_indptr=None):
+        import os
+        self.hbm_indptr = bool(int(os.environ.get("COALA_HBM_INDPTR", "0"))) if hbm_indptr is None else bool(hbm_indptr)
         self.fanouts = [int(f) for f in fanouts]
         self.seed, self.rank, self.calls = int(seed), int(rank), 0
         self._h, self._graph_id, self._max_seeds = None, None, 0
@@ -149,8 +151,16 @@ class MultiLayerNeighborSampler:
         eptr = g.edge_ids.data_ptr() if g.edge_ids is not None else 0
         self._h = check_handle(lib().coala_sampler_create(dev_index, g.indptr.data_ptr(), g.indices.data_ptr(), eptr,
                                                           g.number_of_nodes(), int(n_seeds), fan, len(self.fanouts)), "sampler")
+        if self.hbm_indptr:
+            check(lib().coala_sampler_stage_indptr(self._h), "stage indptr")
         self._graph_id, self._max_seeds = key, int(n_seeds)
         self._device = "cuda:%d" % dev_index
+
+    def trace(self):
+        """Average ms between consecutive enqueued operations (needs COALA_SAMPLER_TRACE=1)."""
+        buf = (C.c_double * 64)()
+        n = lib().coala_sampler_trace(self._h, buf, 64)
+        return [buf[i] for i in range(n)]
 
     def max_sample(self):
         return int(lib().coala_sampler_max_sample(self._h))

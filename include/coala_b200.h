@@ -101,6 +101,13 @@ int coala_cache_row_bytes(coala_cache* c);
  * handle; exchange them with any transport, then attach every peer's. */
 int coala_cache_ipc_handle(coala_cache* c, void* handle64);
 int coala_cache_attach_ipc(coala_cache* c, int peer_local_rank, const void* handle64);
+/* Default sharing of a PARTITIONED shard (n_gpus > 1): the slab is a cuMemCreate allocation exported as
+ * a POSIX file descriptor; send the fd to each peer process (SCM_RIGHTS) and attach it there.  Both
+ * sides map it with 2 MB granularity (a cudaIpcOpenMemHandle import of a multi-GB slab is mapped with
+ * small pages and loses ~3x on random rows).  The caller owns (closes) the descriptors. */
+int coala_cache_is_fd_shared(coala_cache* c);
+int coala_cache_export_fd(coala_cache* c);
+int coala_cache_attach_fd(coala_cache* c, int peer_local_rank, int fd);
 /* same-process attachment (several shards driven from one process, or emulated ranks on one GPU) */
 int coala_cache_attach_local(coala_cache* c, int peer_local_rank, coala_cache* peer);
 
@@ -149,6 +156,14 @@ coala_sampler* coala_sampler_create(int device, uint64_t indptr_ptr, uint64_t in
                                     int64_t num_nodes, int max_seeds, const int* fanouts, int n_layers);
 void coala_sampler_destroy(coala_sampler* s);
 int64_t coala_sampler_max_sample(coala_sampler* s);
+/* B200 option (off by default): keep a private copy of indptr (8(N+1) bytes: 80 MB at 10 M nodes) in
+ * HBM, which removes the first of the two dependent host round trips of every sampled row.  indices
+ * and edge ids stay in pinned host memory. */
+int coala_sampler_stage_indptr(coala_sampler* s);
+/* diagnostics (COALA_SAMPLER_TRACE=1 at creation): average milliseconds between consecutive enqueued
+ * operations of a sample (seed copy, then per layer: reset, sample_rows, scan, compact, flag, scan,
+ * relabel; finally the count read-back).  Returns the number of intervals written. */
+int coala_sampler_trace(coala_sampler* s, double* avg_ms, int max_n);
 /* enqueue all layers for `ns` seeds (device int64); results stay in the sampler's buffers */
 int coala_sampler_sample_async(coala_sampler* s, uint64_t seeds_dev_ptr, int ns, uint64_t rng_key, void* stream);
 /* after the stream is synchronised: counts[2*L+1] = n_src(l), n_edges(l) for l = 0..L-1 in

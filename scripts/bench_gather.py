@@ -124,11 +124,33 @@ def mixed(frac, parity=None):
         out.append(b)
     return out
 
+
+
+def clustered(n_lists, seed=5):
+    """id lists shaped like a sampled mini-batch on a graph with id-local communities: ~1000 centres,
+    each with ~25 ids within +-4096 (unique inside a list)"""
+    r = np.random.default_rng(seed)
+    out = []
+    for _ in range(n_lists):
+        c = r.integers(0, N, size=R // 20)
+        ids = (c[:, None] + r.integers(-4096, 4097, size=(len(c), 40))).ravel()
+        ids = np.unique(np.clip(ids, 0, N - 1))
+        r.shuffle(ids)
+        out.append(np.ascontiguousarray(ids[:R]).astype(np.int64))
+    return out
+
+
 D0 = per_device(0)
 # ---- isolated
 iso = Isolated_Cache(D0["ctrl"], D0["nd"], 0, 1, args.cache_mb, host.data_ptr())
 timed("iso_cold", [(D0, iso)], [batches], iters=nb)
 timed("iso_hit", [(D0, iso)], [batches], iters=args.iters)
+seq = [np.arange(i * R, (i + 1) * R, dtype=np.int64) for i in range(4)]  # contiguous ids: adjacent sets, same way
+timed("iso_seq_warm", [(D0, iso)], [seq], iters=len(seq))
+timed("iso_seq_hit", [(D0, iso)], [seq], iters=8)
+cl = clustered(6)
+timed("iso_clustered_warm", [(D0, iso)], [cl], iters=len(cl))
+timed("iso_clustered_hit", [(D0, iso)], [cl], iters=len(cl))
 for f in (0.01, 0.03, 0.10):
     timed("iso_miss%02d" % int(f * 100), [(D0, iso)], [mixed(f)], iters=args.iters)
 del iso
@@ -163,6 +185,12 @@ if args.gpus >= 2:
     timed("p2p_cold_one", [(D0, caches[0])], [batches], iters=nb)
     timed("p2p_hit_one", [(D0, caches[0])], [batches], iters=args.iters)
     timed("p2p_hit_both", [(D0, caches[0]), (D1, caches[1])], [batches, b1], iters=args.iters)
+    timed("p2p_seq_warm", [(D0, caches[0]), (D1, caches[1])], [seq, seq[::-1]], iters=len(seq))
+    timed("p2p_seq_hit_both", [(D0, caches[0]), (D1, caches[1])], [seq, seq[::-1]], iters=8)
+    cl0, cl1 = clustered(6, 7), clustered(6, 8)
+    timed("p2p_clustered_warm", [(D0, caches[0]), (D1, caches[1])], [cl0, cl1], iters=6)
+    timed("p2p_clustered_hit_both", [(D0, caches[0]), (D1, caches[1])], [cl0, cl1], iters=6)
+    timed("p2p_clustered_hit_one", [(D0, caches[0])], [cl0], iters=6)
     for f in (0.01, 0.03, 0.10):
         timed("p2p_miss%02d_both" % int(f * 100), [(D0, caches[0]), (D1, caches[1])], [mixed(f), mixed(f)], iters=args.iters)
     odd = [np.ascontiguousarray(perm[perm % 2 == 1][i * R:(i + 1) * R]).astype(np.int64) for i in range(min(4, (N // 2) // R))]
