@@ -31,7 +31,7 @@ METRIC = "mini-batches/s (IGB-medium-shaped synthetic graph, SAGE fan-out 5,5, b
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--steps", type=int, default=500)
     p.add_argument("--warmup", type=int, default=20)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--shape", default=os.environ.get("COALA_BENCH_SHAPE", "igb-medium"))
@@ -302,36 +302,51 @@ def run_ours(args):
     eh, em, eb = cache.stats(reset=True)
     e2e_value = N * args.steps / e2e_s
     L = comm.local_size
-    h2d = B * 8 + (B * L * 8 if comm.is_master else 0) + (nd.meta_len * 4 * comm.num_master_process) / 1.0  # seeds + seed slice staging + metadata
-    d2h = B * 8 + (B * L * 8 if comm.is_master else 0) + 8 * (2 * len(fan) + 1) + nd.meta_len * 4 / args.refresh_counter
+    # per step and rank: seeds H2D through the pinned staging buffer; D2H of the block counts, of the step header the loop
+    # reads back, and (every refresh_counter steps) of the cache colour histogram
+    h2d = B * 8
+    d2h = B * 8 + 8 * (2 * len(fan) + 1) + nd.meta_len * 4 / args.refresh_counter
 
     hs, ms_, bs = sum_over_ranks(comm, [h, m, b], device)
     out = None
     if comm.global_rank == 0:
+        # per-link algorithmic bytes of one gather launch: a row is 2R of HBM traffic (line read +
+        # output write on a hit, line write + output write on a miss), R over the host link on a miss, and R over
+        # NVLink into this GPU when its owner is a peer (fraction (G-1)/G of the rows under id % G routing)
         miss_rows = (m + b) / args.steps
-        alg_hbm = 2.0 * R * rows  # 2R per gathered row (line->out on a hit, line+out written on a miss)
-        alg_host = R * miss_rows
-        t_hbm, t_host = alg_hbm / (hbm_peak * 1e9), alg_host / (host_peak * 1e9)
+        G = comm.local_size if args.cache_backend in ("nvshmem", "p2p") else 1
+        remote = (G - 1) / G
+        alg = {"hbm": 2.0 * R * rows, "host_link": R * miss_rows, "nvlink_in": R * (rows - miss_rows) * remote}
+        nvl_peak = 770.0  # measured peer-copy figure of B200_PROFILING.md (900 nominal); scripts/bench_gather.py reads 777 with a kernel
+        peaks = {"hbm": hbm_peak, "host_link": host_peak, "nvlink_in": nvl_peak}
+        srcs = {"hbm": peak_src, "host_link": "coala_probe_read_bandwidth (UVA streaming read, this run)",
+                "nvlink_in": "B200_PROFILING.md measured peer copy"}
         t_meas = gather_ms * 1e-3
-        binding = "host_link" if t_host > t_hbm else "hbm"
+        links = {k: {"achieved": alg[k] / t_meas / 1e9, "peak": peaks[k], "unit": "GB/s", "frac": alg[k] / t_meas / 1e9 / peaks[k],
+                     "alg_bytes_per_launch": alg[k], "peak_source": srcs[k]} for k in alg}
+        binding = max(alg, key=lambda k: alg[k] / peaks[k])  # the link with the largest lower bound on the kernel's time
+        hbm_replay = 2.0 * R * n_last / (replay_ms * 1e-3) / 1e9
         out = {
             "metric": METRIC, "value": value, "unit": "mini-batches/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "ours",
             "config": {"workload": "%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), SAGE fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
                        % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, B, args.cache_size, args.cache_backend, comm.num_master_process, L, args.distribution),
-                       "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (> 126 MB L2, no reuse between steps)" % (rows * R / 1e6),
+                       "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (a different row set every step; the table is %.0f GB, L2 is 126 MB)" % (rows * R / 1e6, ds.num_nodes * R / 1e9),
                        "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter,
                        "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr copy in HBM" if args.hbm_indptr else "")},
             "hit_ratio": hs / max(1.0, hs + ms_ + bs), "rows_per_step": rows,
             "gather_GBs": rows * R / t_meas / 1e9, "sample_stream_ms": sample_ms,
-            "gather_replay": {"ms": replay_ms, "rows": n_last, "out_GBs": n_last * R / replay_ms / 1e6, "hit_ratio": rh / max(1, rh + rm + rb)},
-            "roofline": {"bound": "hbm", "achieved": alg_hbm / t_meas / 1e9, "peak": hbm_peak, "unit": "GB/s", "frac": alg_hbm / t_meas / 1e9 / hbm_peak,
-                         "traffic": None, "peak_source": peak_src, "kernel": "coala_gather_kernel", "kernel_ms": gather_ms,
-                         "kernel_share_of_step": gather_ms / (dev_ms / args.steps),
-                         "binding_link": binding, "binding_frac": max(t_hbm, t_host) / t_meas,
-                         "host_link": {"achieved": alg_host / t_meas / 1e9, "peak": host_peak, "unit": "GB/s", "frac": alg_host / t_meas / 1e9 / host_peak,
-                                       "peak_source": "coala_probe_read_bandwidth (UVA streaming read, this run)"}},
+            # the dominant kernel against the link that bounds it (T_bound = max over links of bytes/peak);
+            # `hbm` is always listed too, and `all_hit_replay` times the same kernel on resident rows (the HBM / NVLink regime)
+            "roofline": {"bound": binding, "achieved": links[binding]["achieved"], "peak": links[binding]["peak"], "unit": "GB/s",
+                         "frac": links[binding]["frac"], "traffic": None, "peak_source": links[binding]["peak_source"],
+                         "kernel": "coala_gather_kernel", "kernel_ms": gather_ms, "kernel_share_of_step": gather_ms / (dev_ms / args.steps),
+                         "links": links,
+                         "all_hit_replay": {"ms": replay_ms, "rows": n_last, "hit_ratio": rh / max(1, rh + rm + rb),
+                                            "hbm": {"achieved": hbm_replay, "peak": hbm_peak, "frac": hbm_replay / hbm_peak},
+                                            "nvlink_in": {"achieved": R * n_last * remote / (replay_ms * 1e-3) / 1e9, "peak": nvl_peak,
+                                                          "frac": R * n_last * remote / (replay_ms * 1e-3) / 1e9 / nvl_peak}}},
             "e2e": {"value": e2e_value, "unit": "mini-batches/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                     "host_link_feature_bytes_per_step": int(R * (em + eb) / args.steps), "hit_ratio": eh / max(1, eh + em + eb),
                     "api": "COALA_GNN_DataLoader.__next__"},

@@ -112,17 +112,26 @@ class MPI_Comm_Manager(object):
         dist.barrier()
 
     def gather_cache_meta(self, gpu_cache_meta, gathered_data):
-        """SUM over the domain, then all-gather across domain masters (S/Shared_Tensor.py:96-100)."""
+        """SUM over the domain, then all-gather across domain masters (S/Shared_Tensor.py:96-100); the gathered
+        histograms are then broadcast inside each domain so that every rank can run the (deterministic)
+        distributor itself instead of receiving its seeds from the master every batch."""
         if self.global_size == 1:
             gathered_data[0].copy_(gpu_cache_meta)
             return
         if self.local_size > 1:
             dist.all_reduce(gpu_cache_meta, op=dist.ReduceOp.SUM, group=self.local_gloo_gather)
+        if self.num_master_process == 1:
+            gathered_data[0].copy_(gpu_cache_meta)
+            return
         if self.is_master:
-            if self.num_master_process > 1:
-                dist.all_gather(gathered_data, gpu_cache_meta, group=self.master_gloo_gather)
-            else:
-                gathered_data[0].copy_(gpu_cache_meta)
+            dist.all_gather(gathered_data, gpu_cache_meta, group=self.master_gloo_gather)
+        if self.local_size > 1:
+            flat = torch.stack(gathered_data) if self.is_master else torch.empty((len(gathered_data),) + tuple(gathered_data[0].shape),
+                                                                                  dtype=gathered_data[0].dtype)
+            dist.broadcast(flat, src=self.master_process_id, group=self.local_gloo_gather)
+            if not self.is_master:
+                for dst, src in zip(gathered_data, flat):
+                    dst.copy_(src)
 
     def broadcast_training_nodes(self, parsed_training_node_list):
         """(S/Shared_Tensor.py:102-103)"""

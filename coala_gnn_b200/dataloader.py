@@ -8,9 +8,16 @@ from .manager import COALA_GNN_Manager
 
 
 class COALA_GNN_Node_Distribution_Scheduler(object):
-    """S/COALA_GNN_DataLoader.py:8-75. Distribution of batch t+1 runs on a thread during batch t
-    (the C ABI call releases the GIL); cache colour metadata is refreshed every `refresh_counter`
-    batches into a double buffer."""
+    """S/COALA_GNN_DataLoader.py:8-75.  Same interface (run(is_last) -> this rank's seeds of the next batch,
+    cache colour metadata refreshed every `refresh_counter` batches into a double buffer, gloo collectives on
+    a background thread), different plumbing:
+      * the reference distributes on the domain master (a CPU loop on a thread) and gloo-broadcasts the
+        domain's seeds to its ranks every batch.  The GPU distributor is deterministic and takes tens of
+        microseconds, so every rank runs it on the same inputs and slices its own seeds: no per-batch
+        collective, no per-batch thread.  For that the refreshed metadata is made identical on all ranks
+        of the domain (MPI_Comm_Manager.gather_cache_meta broadcasts what the masters gathered);
+      * the one-batch-ahead overlap the reference gets from its thread comes from the loader's prefetch
+        (run() for batch t+1 is called while batch t is in flight)."""
 
     def __init__(self, node_distributor, ssd_gnn_manager, refresh_counter=8):
         self.node_distributor = node_distributor
@@ -18,23 +25,13 @@ class COALA_GNN_Node_Distribution_Scheduler(object):
         self.metadata_reuse_counter = 0
         self.refresh_counter = refresh_counter
         self.cache_color_gathered_header = 0
-        self.distribute_thread = None
         self.cache_meta_gather_thread = None
         self.cache_meta_tensor = torch.zeros(self.node_distributor.meta_len, dtype=torch.int32)
 
     def run(self, is_last: bool):
         nd = self.node_distributor
         comm = nd.comm_manager
-        if comm.is_master:
-            if self.distribute_thread is None:  # first stage of the pipeline (:31-35)
-                self.distribute_thread = threading.Thread(target=nd.parse_domain_training_nodes, args=(self.cache_color_gathered_header,))
-                self.distribute_thread.start()
-            self.distribute_thread.join()
-            self.distribute_thread = None
-
-        distributed_node_index = nd.parsed_training_nodes_buffer[nd.parsed_training_nodes_buffer_header]
-        comm.broadcast_training_nodes(distributed_node_index)
-        nd.parsed_training_nodes_buffer_header = (nd.parsed_training_nodes_buffer_header + 1) % 2
+        distributed_node_index = nd.parse_domain_training_nodes(self.cache_color_gathered_header)
 
         if self.metadata_reuse_counter == self.refresh_counter:  # (:46-59)
             self.metadata_reuse_counter = 0
@@ -46,19 +43,13 @@ class COALA_GNN_Node_Distribution_Scheduler(object):
             self.cache_meta_gather_thread = threading.Thread(target=nd.gather_cache_meta, args=(self.cache_meta_tensor,))
             self.cache_meta_gather_thread.start()
 
-        if comm.is_master and not is_last:  # (:64-68)
-            self.distribute_thread = threading.Thread(target=nd.parse_domain_training_nodes, args=(self.cache_color_gathered_header,))
-            self.distribute_thread.start()
-
         self.metadata_reuse_counter += 1
         lr = comm.local_rank
         return distributed_node_index[(lr * nd.batch_size):((lr + 1) * nd.batch_size)]  # (:71-75)
 
     def drain(self):
-        for t in (self.distribute_thread, self.cache_meta_gather_thread):
-            if t is not None:
-                t.join()
-        self.distribute_thread = None
+        if self.cache_meta_gather_thread is not None:
+            self.cache_meta_gather_thread.join()
         self.cache_meta_gather_thread = None
 
 
@@ -103,6 +94,7 @@ class COALA_GNN_DataLoader(object):
             from .pipeline import BatchEngine
             self.engine = BatchEngine(graph, graph_sampler, self.COALA_GNN_Manager, batch_size, device)
         self._epoch_base = 0  # engine batch index of this epoch's first batch
+        self.copy_blocks = False  # True: every batch owns its id/edge tensors (one clone per array, like DGL)
 
     def __iter__(self):
         return self
@@ -146,7 +138,8 @@ class COALA_GNN_DataLoader(object):
         self.counter += 1
         slot = eng.slot_of(self._epoch_base + i)
         torch.cuda.current_stream().wait_event(slot.ev_sampled)
-        input_nodes, output_nodes, blocks = slot.sampler.collect()
+        # views into the slot's buffers: valid until two more batches have been drawn (the slot is then resampled)
+        input_nodes, output_nodes, blocks = slot.sampler.collect(copy=self.copy_blocks)
         eng.wait(self._epoch_base + i)
         return input_nodes, output_nodes, blocks, slot.out[:input_nodes.numel()]
 

@@ -49,6 +49,13 @@ class Node_Distributor(object):
             self.parsed_training_nodes_buffer[h] = self.index_tensor[lo:lo + self.domain_batch_size]
             self.index_offset += self.global_batch_size
             return self.parsed_training_nodes_buffer[h]
+        elif self.parsing_method == "node_color" and self.comm_manager.num_master_process == 1:
+            # one domain: every score is >= 0 > -1 until the single bucket is full and the bucket holds exactly
+            # the batch, so the greedy loop (M/node_distributor_pybind.cuh:150-222) returns the seeds in arrival order
+            lo = self.index_offset
+            self.parsed_training_nodes_buffer[h] = self.index_tensor[lo:lo + self.domain_batch_size]
+            self.index_offset += self.global_batch_size
+            return self.parsed_training_nodes_buffer[h]
         elif self.parsing_method == "node_color":  # (:49-58)
             gather_ptr = [gt.data_ptr() for gt in self.cache_color_double_buffer[color_buf_read_header]]
             self.distribute_manager.distribute_node_with_affinity(self.index_offset, self.parsed_training_nodes_buffer[h].data_ptr(),

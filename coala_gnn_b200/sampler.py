@@ -180,25 +180,41 @@ class MultiLayerNeighborSampler:
         check(lib().coala_sampler_layer_ptrs(self._h, 0, C.byref(src), None, None, None))
         return src.value, int(lib().coala_sampler_input_count_dev_ptr(self._h))
 
-    def collect(self, copy=True):
-        """Wait for the last sample_async and wrap the buffers. copy=False returns views that the next
-        sample overwrites."""
+    def _wrap_buffers(self):
+        """Full-capacity torch views of the sampler's device buffers, built once (collect() then only slices)."""
         import torch
+        L = len(self.fanouts)
+        ns = [self._max_seeds]
+        ne = []
+        for f in reversed(self.fanouts):  # sampling order
+            ne.append(ns[-1] * f)
+            ns.append(ns[-1] + ne[-1])
+        self._views = []
+        for k in range(L):  # reference block order: k = 0 is the input layer = last sampled round
+            l = L - 1 - k
+            p = [C.c_uint64() for _ in range(4)]
+            check(lib().coala_sampler_layer_ptrs(self._h, k, *[C.byref(x) for x in p]))
+            caps = (ns[l + 1], ne[l], ne[l], ne[l])
+            self._views.append([tensor_from_ptr(ptr.value, (cap,), torch.int64, self._device, owner=self) for ptr, cap in zip(p, caps)])
+
+    def collect(self, copy=True):
+        """Wait for the last sample_async and wrap the buffers. copy=False returns views that a later
+        sample with this sampler object overwrites."""
         L = len(self.fanouts)
         counts = (C.c_int64 * (2 * L + 1))()
         check(lib().coala_sampler_counts(self._h, counts), "sampler counts")
+        if getattr(self, "_views_for", None) != self._h:
+            self._wrap_buffers()
+            self._views_for = self._h
         g = self._last_g
         blocks = []
         for k in range(L):
             n_src, ne = counts[2 * k], counts[2 * k + 1]
             n_dst = counts[2 * (k + 1)] if k + 1 < L else counts[2 * L]
-            p = [C.c_uint64() for _ in range(4)]
-            check(lib().coala_sampler_layer_ptrs(self._h, k, *[C.byref(x) for x in p]))
-            ts = []
-            for ptr, n in zip(p, (n_src, ne, ne, ne)):
-                t = tensor_from_ptr(ptr.value, (n,), torch.int64, self._device, owner=self) if n > 0 else \
-                    torch.empty(0, dtype=torch.int64, device=self._device)
-                ts.append(t.clone() if copy else t)
+            v = self._views[k]
+            ts = [v[0][:n_src], v[1][:ne], v[2][:ne], v[3][:ne]]
+            if copy:
+                ts = [t.clone() for t in ts]
             blocks.append(Block(g, ts[0], n_dst, ts[1], ts[2], ts[3]))
         return blocks[0].src_nodes, blocks[-1].dst_nodes, blocks
 
