@@ -133,12 +133,12 @@ class COALA_GNN_DataLoader(object):
         eng.consumer_checkpoint()
         if getattr(self, "_launched", 0) <= i:
             self._launch(i)
-        if self._launched <= i + 1 and i + 1 < self.total_count:
-            self._launch(i + 1)  # prefetch: sampled while batch i is gathered and consumed
+        while self._launched <= i + eng.depth and self._launched < self.total_count:
+            self._launch(self._launched)  # prefetch: sampled while batch i is gathered and consumed
         self.counter += 1
         slot = eng.slot_of(self._epoch_base + i)
         torch.cuda.current_stream().wait_event(slot.ev_sampled)
-        # views into the slot's buffers: valid until two more batches have been drawn (the slot is then resampled)
+        # views into the slot's buffers: valid until `engine.depth` more batches have been drawn (the slot is then resampled)
         input_nodes, output_nodes, blocks = slot.sampler.collect(copy=self.copy_blocks)
         eng.wait(self._epoch_base + i)
         return input_nodes, output_nodes, blocks, slot.out[:input_nodes.numel()]

@@ -57,8 +57,14 @@ class COALA_GNN_Manager(object):
         self._out = [torch.empty((self.max_sample_size, dim), dtype=torch.float32, device=device) for _ in range(2)]
         self._flip = 0
 
+    def out_buffers(self, n):
+        """Persistent output row buffers (one per in-flight batch of the prefetch engine)."""
+        while len(self._out) < n:
+            self._out.append(torch.empty((self.max_sample_size, self.dim), dtype=torch.float32, device=self.device))
+        return self._out[:n]
+
     def _next_out(self, n):
-        self._flip ^= 1
+        self._flip = (self._flip + 1) % 2
         return self._out[self._flip][:n]
 
     def fetch_feature_async(self, index, n_upper, n_dev_ptr, stream):

@@ -29,6 +29,8 @@ class _Slot(object):
         self.seeds = torch.zeros(batch_size, dtype=torch.int64, device=device)
         self.seeds_pin = torch.zeros(batch_size, dtype=torch.int64).pin_memory()
         self.out = out
+        # sampling kernels are small and latency bound: high priority so that they take SM slots as gather CTAs retire
+        self.stream = torch.cuda.Stream(device=device, priority=-1)
         self.ev_sampled = torch.cuda.Event()
         self.ev_gathered = torch.cuda.Event()
         self.t0 = torch.cuda.Event(enable_timing=True)
@@ -38,17 +40,25 @@ class _Slot(object):
 
 
 class BatchEngine(object):
-    """launch(t, seed_fn) enqueues batch t; wait(t) makes the current stream wait for its rows."""
+    """launch(t, seed_fn) enqueues batch t; wait(t) makes the current stream wait for its rows.
+    `depth` batches can be in flight behind the one being consumed (depth + 1 slots).  Each slot samples on
+    its own stream: a sample is a dependent chain of small kernels and host round trips that leaves the GPU
+    and the host link mostly idle, so two of them overlap almost perfectly; gathers run in batch order on
+    one stream."""
 
-    def __init__(self, graph, sampler, manager, batch_size, device, record_gather_events=False):
+    def __init__(self, graph, sampler, manager, batch_size, device, record_gather_events=False, depth=None):
         self.g, self.mgr, self.device = graph, manager, device
         self.seed, self.rank = sampler.seed, sampler.rank
         self.fanouts = list(sampler.fanouts)
-        # sampling kernels are small and latency bound: high priority so that they take SM slots as gather CTAs retire
-        self.s_sample = torch.cuda.Stream(device=device, priority=-1)
+        import os
+        if depth is None:
+            depth = int(os.environ.get("COALA_PREFETCH_DEPTH", "2"))
+        self.depth = max(1, int(depth))
+        self.nslots = self.depth + 1
         self.s_gather = torch.cuda.Stream(device=device)
         self.ev_consumed = torch.cuda.Event()
-        self.slots = [_Slot(k, self.fanouts, batch_size, manager._out[k], device, getattr(sampler, "hbm_indptr", None)) for k in range(2)]
+        outs = manager.out_buffers(self.nslots)
+        self.slots = [_Slot(k, self.fanouts, batch_size, outs[k], device, getattr(sampler, "hbm_indptr", None)) for k in range(self.nslots)]
         for s in self.slots:
             s.sampler._ensure(graph, batch_size)
         self.record = record_gather_events
@@ -61,8 +71,8 @@ class BatchEngine(object):
         self.ev_consumed.record(torch.cuda.current_stream())
 
     def launch(self, t, seed_fn):
-        slot = self.slots[t & 1]
-        ss, sg = self.s_sample, self.s_gather
+        slot = self.slots[t % self.nslots]
+        ss, sg = slot.stream, self.s_gather
         ss.wait_event(self.ev_consumed)
         if slot.used:
             ss.wait_event(slot.ev_gathered)  # the previous gather of this slot read the sampler's id list
@@ -77,7 +87,7 @@ class BatchEngine(object):
                 self.sample_times.append((s0, s1))
             slot.ev_sampled.record(ss)
         sg.wait_event(slot.ev_sampled)
-        sg.wait_event(self.ev_consumed)      # the rows of batch t-2 (same buffer) are no longer needed
+        sg.wait_event(self.ev_consumed)      # the rows of the batch that used this buffer before are no longer needed
         idx_ptr, n_ptr = slot.sampler.input_nodes_dev_ptrs()
         with torch.cuda.stream(sg):
             if self.record:
@@ -94,7 +104,7 @@ class BatchEngine(object):
         return slot
 
     def slot_of(self, t):
-        slot = self.slots[t & 1]
+        slot = self.slots[t % self.nslots]
         assert slot.batch == t, "batch %d is not in flight" % t
         return slot
 
@@ -119,7 +129,7 @@ class DevicePipeline(object):
     `refresh_counter` batches and stays on the device.  step() returns the rows of batch t (valid on
     the current stream) while batch t+1 is already in flight."""
 
-    def __init__(self, loader, record_gather_events=False, prefetch=True, seed=None):
+    def __init__(self, loader, record_gather_events=False, prefetch=True, seed=None, depth=None):
         self.loader = loader
         self.nd = loader.node_distributor
         self.comm = self.nd.comm_manager
@@ -130,10 +140,10 @@ class DevicePipeline(object):
         if self.comm.num_master_process != 1:
             raise NotImplementedError("DevicePipeline drives one cache domain; use the drop-in loader for D > 1")
         self.B, self.L = self.nd.batch_size, self.comm.local_size
-        self.engine = BatchEngine(self.g, loader.sampler, self.mgr, self.B, self.device, record_gather_events)
+        self.engine = BatchEngine(self.g, loader.sampler, self.mgr, self.B, self.device, record_gather_events, depth=depth if prefetch else 1)
         if seed is not None:
             self.engine.seed = int(seed)
-        self.domain_seeds = [torch.zeros(self.B * self.L, dtype=torch.int64, device=self.device) for _ in range(2)]
+        self.domain_seeds = [torch.zeros(self.B * self.L, dtype=torch.int64, device=self.device) for _ in range(self.engine.nslots)]
         self.meta = torch.zeros(self.nd.meta_len, dtype=torch.int32, device=self.device)
         self.step_idx = 0
         self.refresh = loader.refresh_counter
@@ -150,7 +160,7 @@ class DevicePipeline(object):
             if t % self.refresh == 0 and t > 0:
                 self.refresh_meta(stream)
             if self.nd.parsing_method == "node_color":
-                dom = self.domain_seeds[t & 1]
+                dom = self.domain_seeds[t % self.engine.nslots]
                 self.nd.distribute_manager.distribute_async(offset, dom.data_ptr(), [self.meta.data_ptr()], stream.cuda_stream)
                 return dom[self.comm.local_rank * self.B:(self.comm.local_rank + 1) * self.B]
             lo = offset + self.comm.local_rank * self.B
@@ -170,8 +180,9 @@ class DevicePipeline(object):
         eng.consumer_checkpoint()
         if eng.launched <= t:
             eng.launch(t, self._seed_fn(t))
-        if self.prefetch and eng.launched <= t + 1:
-            eng.launch(t + 1, self._seed_fn(t + 1))
+        if self.prefetch:
+            while eng.launched <= t + eng.depth:
+                eng.launch(eng.launched, self._seed_fn(eng.launched))
         slot = eng.wait(t)
         self.step_idx += 1
         return slot.out
