@@ -326,6 +326,9 @@ def run_ours(args):
                      "alg_bytes_per_launch": alg[k], "peak_source": srcs[k]} for k in alg}
         binding = max(alg, key=lambda k: alg[k] / peaks[k])  # the link with the largest lower bound on the kernel's time
         hbm_replay = 2.0 * R * n_last / (replay_ms * 1e-3) / 1e9
+        # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this same workload
+        # (profiles/r1b_gather_full_raw.csv: 77.1 MB + 88.9 MB); only quoted for the configuration it was captured on
+        traffic = 166.0e6 if (N == 1 and args.shape == "igb-medium" and args.cache_size == 16384 and args.fan_out == "5,5" and B == 1024) else None
         out = {
             "metric": METRIC, "value": value, "unit": "mini-batches/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
@@ -340,7 +343,7 @@ def run_ours(args):
             # the dominant kernel against the link that bounds it (T_bound = max over links of bytes/peak);
             # `hbm` is always listed too, and `all_hit_replay` times the same kernel on resident rows (the HBM / NVLink regime)
             "roofline": {"bound": binding, "achieved": links[binding]["achieved"], "peak": links[binding]["peak"], "unit": "GB/s",
-                         "frac": links[binding]["frac"], "traffic": None, "peak_source": links[binding]["peak_source"],
+                         "frac": links[binding]["frac"], "traffic": traffic, "peak_source": links[binding]["peak_source"],
                          "kernel": "coala_gather_kernel", "kernel_ms": gather_ms, "kernel_share_of_step": gather_ms / (dev_ms / args.steps),
                          "links": links,
                          "all_hit_replay": {"ms": replay_ms, "rows": n_last, "hit_ratio": rh / max(1, rh + rm + rb),

@@ -44,7 +44,7 @@ class BatchEngine(object):
     `depth` batches can be in flight behind the one being consumed (depth + 1 slots).  Each slot samples on
     its own stream: a sample is a dependent chain of small kernels and host round trips that leaves the GPU
     and the host link mostly idle, so two of them overlap almost perfectly; gathers run in batch order on
-    one stream."""
+    one stream.  Measured at igb-small N=1 (sampler-bound): depth 1 / 2 / 3 = 7.7 K / 11.3 K / 13.4 K batches/s."""
 
     def __init__(self, graph, sampler, manager, batch_size, device, record_gather_events=False, depth=None):
         self.g, self.mgr, self.device = graph, manager, device
@@ -52,7 +52,7 @@ class BatchEngine(object):
         self.fanouts = list(sampler.fanouts)
         import os
         if depth is None:
-            depth = int(os.environ.get("COALA_PREFETCH_DEPTH", "2"))
+            depth = int(os.environ.get("COALA_PREFETCH_DEPTH", "3"))
         self.depth = max(1, int(depth))
         self.nslots = self.depth + 1
         self.s_gather = torch.cuda.Stream(device=device)

@@ -156,3 +156,23 @@ def test_npy_loader_error_behaviour(tmp_path):
     np.save(f4, np.zeros(10, dtype=np.float32))
     with pytest.raises(RuntimeError, match="dtype"):
         Node_distributor_pybind(items.ctypes.data, 0, 4, 1, 1, f4, good, good, device=0)
+
+
+def test_npy_streaming_copy_pads_rows(tmp_path):
+    """datasets._copy_npy_into: .npy -> preallocated (row-padded) array in chunks, without loading the file whole."""
+    from coala_gnn_b200.datasets import _copy_npy_into, npy_shape
+    rng = np.random.default_rng(0)
+    a = rng.random((1000, 100)).astype(np.float32)
+    p = str(tmp_path / "a.npy")
+    np.save(p, a)
+    assert npy_shape(p) == ((1000, 100), np.dtype(np.float32))
+    dst = np.zeros((1000, 128), dtype=np.float32)
+    _copy_npy_into(dst, p, threads=3, chunk_rows=77)
+    assert np.array_equal(dst[:, :100], a) and not dst[:, 100:].any()
+    v = np.arange(5000, dtype=np.int64)
+    np.save(p, v)
+    d1 = np.empty(5000, dtype=np.int64)
+    _copy_npy_into(d1, p, threads=2, chunk_rows=999)
+    assert np.array_equal(d1, v)
+    with pytest.raises(ValueError):
+        _copy_npy_into(np.empty(10, dtype=np.int64), p)
