@@ -1,6 +1,6 @@
-"""Multi-process parity check of the N>1 path (run under torchrun, one rank per GPU):
+"""TEST INFRASTRUCTURE (launched by tests/test_gpu_multi.py, or by hand). Multi-process parity check of the N>1 path (run under torchrun, one rank per GPU):
 
-    torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 scripts/check_multi_gpu.py [--gpus_per_domain L]
+    torchrun --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 tests/multi_gpu_check.py [--gpus_per_domain L]
 
 Every rank iterates the drop-in loader over a synthetic graph and checks, per batch: gathered rows bitwise
 equal to the procedural feature table (re-derived on the GPU), input nodes / blocks equal to the oracle's for
@@ -78,4 +78,4 @@ for backend in args.backends.split(","):
 comm.global_comm.Barrier()
 ds.cleanup()
 if comm.global_rank == 0:
-    print("check_multi_gpu: all good")
+    print("multi_gpu_check: all good")
