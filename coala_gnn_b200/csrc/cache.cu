@@ -58,7 +58,9 @@ struct coala_cache {
     bool vmm = false;                    // slab allocated with cuMemCreate (shareable as a POSIX fd)
     VmmRegion region;                    // own slab when vmm
     VmmRegion peer_region[COALA_MAX_GPUS];
-    int copy_engine = 0;
+    int copy_engine = 0;   // 0 = registers, 1 = bulk asynchronous copies (coala_cache_set_copy_engine / COALA_GATHER_ENGINE)
+    int bulk_nbuf = 3;     // row buffers per warp of engine 1 (COALA_GATHER_NBUF = 2|3)
+    int bulk_waves = 2;    // COALA_GATHER_BULK_WAVES
     int waves = 2;
     int ctas_per_sm = 2;   // residency cap of the gather (see launch_gather)
     size_t smem_per_sm = 228 * 1024;
@@ -113,10 +115,44 @@ static int launch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t
     return 0;
 }
 
+// Copy engine 1 (bulk asynchronous copies through shared memory, see cache.cuh).  Two row buffers per warp;
+// the dynamic shared memory doubles as the residency cap (2 CTAs per SM).
+template <int VPL, bool SYS, int NBUF>
+static int launch_gather_bulk(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st) {
+    if (n <= 0) return 0;
+    const int threads = 256, wpb = threads / 32, resident = 2;
+    const size_t need_smem = (size_t)wpb * NBUF * c->row_bytes;
+    size_t smem = (size_t)(c->smem_per_sm / resident) - 16384;
+    if (smem < need_smem) smem = need_smem;
+    COALA_CUDA(cudaFuncSetAttribute(coala_gather_bulk_kernel<VPL, SYS, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int64_t blocks = (int64_t)c->sm_count * resident * c->bulk_waves;
+    const int64_t need = (n + wpb - 1) / wpb;
+    if (blocks > need) blocks = need;
+    coala_gather_bulk_kernel<VPL, SYS, NBUF><<<(unsigned)blocks, threads, smem, st>>>(c->params, idx, out, n, n_dev);
+    COALA_CUDA(cudaGetLastError());
+    return 0;
+}
+
 static int dispatch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
                            bool serial) {
     const bool sys = c->kind == COALA_CACHE_PARTITIONED && c->n_gpus > 1;
     const int vpl = c->row_bytes / 512;
+    // bulk copies need 16-byte aligned output rows of a 16-byte multiple
+    const bool bulk_ok = c->copy_engine == 1 && !serial && (c->params.out_stride * 4) % 16 == 0 && (c->params.out_dim * 4) % 16 == 0 &&
+                         ((uintptr_t)out & 15) == 0;
+    if (bulk_ok) {
+#define COALA_GOB(V)                                                                                                      \
+    if (c->bulk_nbuf == 3)                                                                                                \
+        return sys ? launch_gather_bulk<V, true, 3>(c, idx, out, n, n_dev, st) : launch_gather_bulk<V, false, 3>(c, idx, out, n, n_dev, st); \
+    return sys ? launch_gather_bulk<V, true, 2>(c, idx, out, n, n_dev, st) : launch_gather_bulk<V, false, 2>(c, idx, out, n, n_dev, st)
+        switch (vpl) {
+            case 1: COALA_GOB(1);
+            case 2: COALA_GOB(2);
+            case 4: COALA_GOB(4);
+            case 8: COALA_GOB(8);
+        }
+#undef COALA_GOB
+    }
 #define COALA_GO(V)                                                                                    \
     if (c->min_blocks == 2)                                                                            \
         return sys ? launch_gather<V, true, 2>(c, idx, out, n, n_dev, st, serial)                      \
@@ -202,6 +238,9 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     p.zero = 0;
     if (const char* e = getenv("COALA_GATHER_MINB")) c->min_blocks = atoi(e) == 2 ? 2 : 3;
     if (const char* e = getenv("COALA_GATHER_CTAS_PER_SM")) c->ctas_per_sm = atoi(e);
+    if (const char* e = getenv("COALA_GATHER_ENGINE")) c->copy_engine = atoi(e) == 1 ? 1 : 0;
+    if (const char* e = getenv("COALA_GATHER_NBUF")) c->bulk_nbuf = atoi(e) == 2 ? 2 : 3;
+    if (const char* e = getenv("COALA_GATHER_BULK_WAVES")) c->bulk_waves = atoi(e) > 0 ? atoi(e) : 2;
     if (const char* e = getenv("COALA_GATHER_WAVES")) c->waves = atoi(e) > 0 ? atoi(e) : 2;
 
     cudaDeviceProp prop;
@@ -409,7 +448,7 @@ extern "C" int coala_cache_export_state(coala_cache* c, uint64_t* keys, uint32_t
 }
 
 extern "C" int coala_cache_set_copy_engine(coala_cache* c, int engine) {
-    if (engine != 0) COALA_FAIL("copy engine not available in this build");
+    if (engine != 0 && engine != 1) COALA_FAIL("copy engine must be 0 (registers) or 1 (bulk asynchronous copies)");
     c->copy_engine = engine;
     return 0;
 }

@@ -287,3 +287,157 @@ __global__ void __launch_bounds__(256, MINB) coala_gather_kernel(CacheParams p, 
     __syncthreads();
     if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
 }
+
+// ---------------------------------------------------------------------------------------------
+// Copy engine 1: hit rows move HBM/peer -> shared memory -> output with bulk asynchronous copies
+// (cp.async.bulk, the 1-D TMA path; SASS: UBLKCP) instead of through registers.  One elected lane
+// issues a whole row; NBUF (2 or 3) row buffers per warp keep NBUF row loads in flight while the oldest
+// one is validated and stored (8-12 KB per warp at R = 4 KB, against 4 KB through registers).  The
+// seqlock re-check is ordered behind the data by the mbarrier wait (acquire).  Misses, busy lines and
+// failed validations take the register path of resolve_row.
+// ---------------------------------------------------------------------------------------------
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE_%=;\n"
+        "bra WAIT_%=;\n"
+        "DONE_%=:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_load(void* smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void bulk_store(void* gdst, const void* smem_src, uint32_t bytes) {
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(smem_src)), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_read_all() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+struct BulkPending {   // a hit row whose line is on its way into shared memory
+    uint64_t id, tw;
+    uint32_t set, row;   // row = index into this launch's id list
+    uint32_t meta;       // way | g << 5 | buf << 9  (g < COALA_MAX_GPUS = 16)
+};
+
+template <int VPL, bool SYS, int NBUF>
+__global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p, const int64_t* __restrict__ idx,
+                                                                   float* __restrict__ out, int64_t n,
+                                                                   const int64_t* __restrict__ n_dev) {
+    static_assert(NBUF == 2 || NBUF == 3, "queue below is written for one or two waiting rows");
+    extern __shared__ __align__(128) uint8_t dyn_smem[];
+    __shared__ uint64_t bars[8][NBUF];
+    __shared__ unsigned s_stat[3];
+    const unsigned lane = lane_id();
+    const int wib = threadIdx.x >> 5;
+    uint8_t* mybuf = dyn_smem + (size_t)wib * NBUF * p.row_bytes;
+    if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
+    if (lane == 0) {
+        for (int b = 0; b < NBUF; b++) mbar_init(&bars[wib][b], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async;" ::: "memory");
+    }
+    __syncthreads();
+    if (n_dev) n = min(n, *n_dev);
+    const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
+    const int64_t rpw = (n + warps_total - 1) / warps_total;
+    const int64_t end = min(n, (w + 1) * rpw);
+    const uint32_t out_bytes = (uint32_t)p.out_dim * 4;
+    unsigned n_hit = 0, n_miss = 0, n_byp = 0;
+    unsigned phase_bits = 0;   // bit b = parity the next wait on buffer b expects
+    unsigned cur = 0;          // buffer of the next load
+    BulkPending q0, q1;        // q0 = oldest waiting row, q1 = the one behind it (NBUF == 3)
+    int waiting = 0;
+
+    auto count = [&](int res) { n_hit += res == 0; n_miss += res == 1; n_byp += res == 2; };
+    // finish the oldest waiting row: wait for its line, validate, store from shared memory or fall back
+    auto complete_oldest = [&]() {
+        const unsigned buf = q0.meta >> 9, way = q0.meta & 31u;
+        const int g = (int)((q0.meta >> 5) & 15u);
+        mbar_wait(&bars[wib][buf], (phase_bits >> buf) & 1u);
+        phase_bits ^= 1u << buf;
+        const ShardView& sh = p.shard[g];
+        float* out_row = out + (int64_t)q0.row * (int64_t)p.out_stride;
+        const uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + (uint64_t)q0.set * COALA_WAYS + way);
+        if (t2 == q0.tw) {
+            if (lane == 0) bulk_store(out_row, mybuf + (size_t)buf * p.row_bytes, out_bytes);
+            count(0);
+        } else {  // the line changed under the copy: redo the row through the register path
+            const uint64_t t = ld_relaxed_u64<SYS>(sh.tags + (uint64_t)q0.set * COALA_WAYS + lane);
+            count(resolve_row<VPL, SYS>(p, q0.id, g, q0.set, t, out_row, lane));
+        }
+        q0 = q1;
+        waiting--;
+    };
+
+    for (int64_t base = w * rpw; base < end; base += 32) {
+        const int cnt = (int)min((int64_t)32, end - base);
+        uint64_t my_id = 0;
+        int my_g = p.my_slot;
+        uint32_t my_set = 0;
+        if ((int)lane < cnt) {
+            my_id = (uint64_t)__ldg(idx + base + lane);
+            if (p.route_gpus > 1) my_g = (int)(my_id % (uint64_t)p.route_gpus);
+            my_set = (uint32_t)((my_id / (uint64_t)p.hash_div) % p.num_sets);
+        }
+        uint64_t id = __shfl_sync(0xffffffffu, my_id, 0);
+        int g = __shfl_sync(0xffffffffu, my_g, 0);
+        uint32_t set = __shfl_sync(0xffffffffu, my_set, 0);
+        uint64_t t = ld_relaxed_u64<SYS>(p.shard[g].tags + (uint64_t)set * COALA_WAYS + lane);
+        for (int i = 0; i < cnt; i++) {
+            uint64_t id_n = 0, t_n = 0;
+            int g_n = 0;
+            uint32_t set_n = 0;
+            if (i + 1 < cnt) {
+                id_n = __shfl_sync(0xffffffffu, my_id, i + 1);
+                g_n = __shfl_sync(0xffffffffu, my_g, i + 1);
+                set_n = __shfl_sync(0xffffffffu, my_set, i + 1);
+                t_n = ld_relaxed_u64<SYS>(p.shard[g_n].tags + (uint64_t)set_n * COALA_WAYS + lane);
+            }
+            const unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
+            const unsigned way = m ? __ffs(m) - 1 : 0;
+            const uint64_t tw = __shfl_sync(0xffffffffu, t, way);
+            if (m && ((tw >> TAG_VER_SHIFT) & 1) == 0) {
+                // buffer `cur` belonged to a row completed at least one iteration ago
+                if (lane == 0) {
+                    bulk_wait_read_all();  // ... and the store that drained it has read it
+                    mbar_expect_tx(&bars[wib][cur], p.row_bytes);
+                    bulk_load(mybuf + (size_t)cur * p.row_bytes,
+                              p.shard[g].lines + ((uint64_t)set * COALA_WAYS + way) * (p.row_bytes >> 4), p.row_bytes, &bars[wib][cur]);
+                }
+                if (waiting == NBUF - 1) complete_oldest();
+                BulkPending c;
+                c.id = id; c.tw = tw; c.set = set; c.row = (uint32_t)(base + i);
+                c.meta = way | ((unsigned)g << 5) | (cur << 9);
+                if (waiting == 0) q0 = c; else q1 = c;
+                waiting++;
+                cur = cur + 1 == NBUF ? 0 : cur + 1;
+            } else {
+                count(resolve_row<VPL, SYS>(p, id, g, set, t, out + (base + i) * (int64_t)p.out_stride, lane));
+            }
+            id = id_n; g = g_n; set = set_n; t = t_n;
+        }
+    }
+    while (waiting) complete_oldest();
+    if (lane == 0) {
+        bulk_wait_all();
+        if (n_hit) atomicAdd(&s_stat[0], n_hit);
+        if (n_miss) atomicAdd(&s_stat[1], n_miss);
+        if (n_byp) atomicAdd(&s_stat[2], n_byp);
+    }
+    __syncthreads();
+    if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
+}

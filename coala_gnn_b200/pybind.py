@@ -208,6 +208,10 @@ class _CacheBase:
         check(lib().coala_cache_read_feature_async(self._h, int(out_ptr), int(idx_ptr), int(n), int(n_dev_ptr), stream),
               "read_feature_async")
 
+    def set_copy_engine(self, engine):
+        """0 = rows through registers (16-byte vector loads), 1 = bulk asynchronous copies through shared memory."""
+        check(lib().coala_cache_set_copy_engine(self._h, int(engine)), "set_copy_engine")
+
     def read_feature_serial(self, out_ptr, idx_ptr, n):
         check(lib().coala_cache_read_feature_serial(self._h, int(out_ptr), int(idx_ptr), int(n)), "read_feature_serial")
 

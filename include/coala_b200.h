@@ -135,7 +135,9 @@ int coala_cache_stats(coala_cache* c, uint64_t* hit, uint64_t* miss, uint64_t* b
 int coala_cache_print_stats(coala_cache* c);
 /* test hook: dumps tags (id field, 0xFF.. = empty), colour meta and round-robin pointers */
 int coala_cache_export_state(coala_cache* c, uint64_t* keys, uint32_t* color_meta, uint32_t* set_cnt);
-/* choose the row-copy engine: 0 = 16-byte vector loads (default), 1 = TMA bulk copies */
+/* choose the row-copy engine of the gather: 0 = rows through registers with 16-byte vector loads (default),
+ * 1 = hit rows as bulk asynchronous copies (cp.async.bulk, 1-D TMA) line -> shared memory -> output; rows whose
+ * byte length / stride is not a multiple of 16 keep engine 0.  COALA_GATHER_ENGINE=1 selects it at create time. */
 int coala_cache_set_copy_engine(coala_cache* c, int engine);
 
 /* NCCL all-to-all variant helpers (comparison backend).

@@ -204,7 +204,10 @@ if args.gpus >= 2:
     torch.cuda.set_device(1)
     peer_buf = torch.empty(1 << 30, dtype=torch.uint8, device="cuda:1")
     torch.cuda.set_device(0)
-    torch.cuda.cudart().cudaDeviceEnablePeerAccess(1, 0)  # the shards are VMM mappings; this plain buffer needs classic peer access
+    # the shards are VMM mappings; this plain buffer needs classic peer access, which torch enables on the
+    # first cross-device copy
+    peer_buf[:4096].to("cuda:0")
+    torch.cuda.synchronize()
     check(L.coala_probe_read_bandwidth(peer_buf.data_ptr(), 1 << 30, 5, C.byref(gb)))
     res["nvlink_read_GBs"] = gb.value
 torch.cuda.set_device(0)

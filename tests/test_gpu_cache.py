@@ -63,11 +63,14 @@ def test_isolated_serial_matches_oracle_exactly(dim):
     _check_state_equal(cache, model, C=s["C"])
 
 
+@pytest.mark.parametrize("engine", [0, 1])
 @pytest.mark.parametrize("dim", [128, 1024, 100, 101])
-def test_isolated_parallel_features_bit_exact_and_invariants(dim):
+def test_isolated_parallel_features_bit_exact_and_invariants(dim, engine):
+    """engine 1 = bulk asynchronous copies for hit rows (dim 101 has unaligned rows and must fall back)."""
     from coala_gnn_b200.pybind import Isolated_Cache
     s = _setup(8000, dim)
     cache = Isolated_Cache(s["ctrl"], s["nd"], 0, 1, 2, s["host"].data_ptr())
+    cache.set_copy_engine(engine)
     rng = np.random.default_rng(3)
     total = 0
     for it in range(6):
@@ -89,11 +92,13 @@ def test_isolated_parallel_features_bit_exact_and_invariants(dim):
     assert scnt.sum() == m
 
 
-def test_conflict_storm_single_set_and_empty_batch():
+@pytest.mark.parametrize("engine", [0, 1])
+def test_conflict_storm_single_set_and_empty_batch(engine):
     """Every id maps to the same set (eviction storm) while readers hit it; plus n = 0."""
     from coala_gnn_b200.pybind import Isolated_Cache
     s = _setup(64 * 300, 256)
     cache = Isolated_Cache(s["ctrl"], s["nd"], 0, 1, 1, s["host"].data_ptr())
+    cache.set_copy_engine(engine)
     S = cache.num_sets()
     assert _read(cache, np.zeros(0, dtype=np.int64), 256).shape == (0, 256)
     rng = np.random.default_rng(5)
@@ -105,10 +110,12 @@ def test_conflict_storm_single_set_and_empty_batch():
     assert h + m + b == 5 * 4000
 
 
-def test_warm_cache_all_hits_and_get_cache_data_default_len():
+@pytest.mark.parametrize("engine", [0, 1])
+def test_warm_cache_all_hits_and_get_cache_data_default_len(engine):
     from coala_gnn_b200.pybind import Isolated_Cache
     s = _setup(3000, 128)
     cache = Isolated_Cache(s["ctrl"], s["nd"], 0, 1, 4, s["host"].data_ptr())  # 8192 lines > 3000 nodes
+    cache.set_copy_engine(engine)
     idx = np.random.default_rng(0).permutation(3000)
     _read(cache, idx, 128)
     cache.stats(reset=True)
@@ -149,9 +156,10 @@ def test_partitioned_emulated_ranks_match_oracle(G):
         _check_state_equal(caches[g], model, gpu=g, C=s["C"])
     hm = np.array([c.stats() for c in caches]).sum(axis=0)
     assert (hm[0], hm[1]) == model.stats() and hm[2] == 0
-    # parallel launches through the reference-shaped call pair
+    # parallel launches through the reference-shaped call pair, both copy engines
     import torch
     for g in range(G):
+        caches[g].set_copy_engine(g % 2)
         idx = rng.permutation(9000)[:4000]
         t = torch.from_numpy(idx).cuda()
         out = torch.zeros((4000, 128), device="cuda")
