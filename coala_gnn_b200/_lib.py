@@ -79,6 +79,9 @@ SIGNATURES = {
     "coala_gc_cpu_calculate_color_affinity": (None, [_vp]),
     "coala_gc_get_num_color": (_u64, [_vp]),
     "coala_gc_get_num_color_node": (_u64, [_vp]),
+    "coala_gc_gpu_color_graph_optimized": (_i32, [_vp, _u64, _u64, _i32]),
+    "coala_gc_gpu_calculate_color_affinity": (_i32, [_vp, _i32]),
+    "coala_gc_get_hops": (_i32, [_vp, _u64]),
     "coala_synth_fill_features": (_i32, [_u64, _u64, _i64, _i64, _i32, _i64, _vp]),
     "coala_synth_check_rows": (_i32, [_u64, _u64, _i64, _i32, _i64, _u64, _vp]),
     "coala_probe_read_bandwidth": (_i32, [_u64, _i64, _i32, _vp]),

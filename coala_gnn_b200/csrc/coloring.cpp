@@ -12,6 +12,7 @@
 // no hop (:158-159) — the hop buffer is zero-initialised here (the reference leaves it
 // uninitialised, :331; fresh pages read as 0).
 #include "../../include/coala_b200.h"
+#include "coloring.h"
 #include <algorithm>
 #include <cmath>
 #include <cstdint>
@@ -19,21 +20,6 @@
 #include <unordered_map>
 #include <utility>
 #include <vector>
-
-struct coala_gc {
-    uint64_t num_nodes = 0, num_colored = 0, next_color = 1;
-    int max_hop = 10;            // global_max_hop (M/graph_coloring.h:19)
-    float base_rate = 0.005f;    // global_sampling_rate (:20)
-    int topk = 10;               // (:22)
-    uint64_t* color = nullptr;
-    uint64_t* topk_color = nullptr;
-    double* topk_aff = nullptr;
-    const uint64_t* indptr = nullptr;
-    const uint64_t* indices = nullptr;
-    std::vector<uint16_t> hop;
-    std::vector<uint8_t> is_train;
-    std::vector<std::pair<uint64_t, uint64_t>> work[2];  // (node, colour)
-};
 
 namespace {
 
@@ -84,6 +70,18 @@ void group_by_color(const coala_gc* g, uint64_t num_c, std::vector<uint64_t>& st
 
 }  // namespace
 
+void coala_gc_draw_train_seeds(coala_gc* g, const int64_t* train, uint64_t n_train) {
+    for (uint64_t t = 0; t < n_train; t++) g->is_train[train[t]] = 1;                        // (:99-105)
+    const double frac = std::min(20.0, (double)g->num_nodes / (double)n_train);               // (:77)
+    const double rate = g->base_rate * frac;                                                  // (:78) float * double
+    for (uint64_t t = 0; t < n_train; t++) {                                                  // (:81-92)
+        const int64_t v = train[t];
+        if (g->color[v] != 0) continue;
+        float samp = static_cast<float>(rand()) / RAND_MAX;
+        if (samp <= rate) g->work[0].emplace_back((uint64_t)v, g->next_color++);
+    }
+}
+
 extern "C" {
 
 coala_gc* coala_gc_create(uint64_t num_nodes) {
@@ -93,7 +91,10 @@ coala_gc* coala_gc_create(uint64_t num_nodes) {
     g->is_train.assign(num_nodes, 0);
     return g;
 }
-void coala_gc_destroy(coala_gc* g) { delete g; }
+void coala_gc_destroy(coala_gc* g) {
+    if (g) coala_gc_gpu_release(g);
+    delete g;
+}
 void coala_gc_set_adj_csc(coala_gc* g, uint64_t indptr, uint64_t indices) {
     g->indptr = reinterpret_cast<const uint64_t*>(indptr);
     g->indices = reinterpret_cast<const uint64_t*>(indices);
@@ -119,15 +120,7 @@ void coala_gc_cpu_color_graph(coala_gc* g) {
 // cpu_color_graph_optimized (M/graph_coloring.cpp:108-160)
 void coala_gc_cpu_color_graph_optimized(coala_gc* g, uint64_t train_ptr, uint64_t n_train) {
     const int64_t* train = reinterpret_cast<const int64_t*>(train_ptr);
-    for (uint64_t t = 0; t < n_train; t++) g->is_train[train[t]] = 1;                        // (:99-105)
-    const double frac = std::min(20.0, (double)g->num_nodes / (double)n_train);               // (:77)
-    const double rate = g->base_rate * frac;                                                  // (:78) float * double
-    for (uint64_t t = 0; t < n_train; t++) {                                                  // (:81-92)
-        const int64_t v = train[t];
-        if (g->color[v] != 0) continue;
-        float samp = static_cast<float>(rand()) / RAND_MAX;
-        if (samp <= rate) g->work[0].emplace_back((uint64_t)v, g->next_color++);
-    }
+    coala_gc_draw_train_seeds(g, train, n_train);
     int hop = 0;
     for (; hop < g->max_hop; hop++) {
         const int cur = hop % 2, nxt = (hop + 1) % 2;

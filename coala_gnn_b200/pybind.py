@@ -410,6 +410,20 @@ class Graph_Coloring:
     def cpu_calculate_color_affinity(self):
         lib().coala_gc_cpu_calculate_color_affinity(self._h)
 
+    # GPU mode (not in the reference): same seeds / colour ids, level-synchronous traversal and sort-based
+    # affinity on the device; see include/coala_b200.h
+    def gpu_color_graph_optimized(self, train_ptr, n_train, device=0):
+        check(lib().coala_gc_gpu_color_graph_optimized(self._h, int(train_ptr), int(n_train), int(device)), "gpu_color_graph_optimized")
+
+    def gpu_calculate_color_affinity(self, device=0):
+        check(lib().coala_gc_gpu_calculate_color_affinity(self._h, int(device)), "gpu_calculate_color_affinity")
+
+    def get_hops(self, num_nodes):
+        import numpy as np
+        hop = np.zeros(int(num_nodes), dtype=np.uint16)
+        check(lib().coala_gc_get_hops(self._h, hop.ctypes.data), "get_hops")
+        return hop
+
     def get_num_color(self):
         return int(lib().coala_gc_get_num_color(self._h))
 

@@ -199,6 +199,18 @@ void coala_gc_cpu_count_nearest_color_less_memory(coala_gc* g);
 void coala_gc_cpu_calculate_color_affinity(coala_gc* g);
 uint64_t coala_gc_get_num_color(coala_gc* g);
 uint64_t coala_gc_get_num_color_node(coala_gc* g);
+/* GPU mode (the cpu_* functions above stay the bit-exact reference mode).
+ * gpu_color_graph_optimized: same seeds and colour ids as cpu_color_graph_optimized (M/graph_coloring.cpp:77-92, host
+ * rand() stream), traversal as a level-synchronous multi-source search on `device` (smallest colour id wins a contested
+ * node; the reference's winner depends on its LIFO visit order, :143-157).
+ * gpu_calculate_color_affinity: cpu_calculate_color_affinity (:254-294) for whatever colouring / hops the object holds
+ * (from either mode): per-(colour, neighbour colour, hop) edge counts by radix sort, score = sum_h count_h * exp(-0.5 h),
+ * top-k by (score desc, colour asc), divided by the colour's in-edge count.  Scores agree with the host mode to ~1e-15
+ * relative (summation order), top-k lists agree wherever scores are not tied.  Both return 0 or -1 (coala_last_error). */
+int coala_gc_gpu_color_graph_optimized(coala_gc* g, uint64_t train_ptr, uint64_t n_train, int device);
+int coala_gc_gpu_calculate_color_affinity(coala_gc* g, int device);
+/* test hook: hop (level) per node as uint16, 0 = none */
+int coala_gc_get_hops(coala_gc* g, uint64_t dst_u16_ptr);
 
 /* ------------------------------------------------------------------ synthetic data + checks (GPU) */
 /* feat[r, c] = hash(seed, row0 + r, c) in [0,1), written through a device-visible address */

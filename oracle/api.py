@@ -9,7 +9,7 @@ from . import lib, ref, _p, _u64, _vp
 __all__ = [
     "mix64", "fill_features", "distribute", "ref_distribute", "CacheModel", "sample_layer",
     "to_block", "sample_blocks_detailed", "sample_blocks_fast", "index_select", "ref_color_graph",
-    "layer_key", "batch_key",
+    "layer_key", "batch_key", "draw_train_seeds", "levelsync_color_graph", "affinity_from_counts",
 ]
 
 C1 = 0xA24BAED4963EE407
@@ -195,3 +195,102 @@ def ref_color_graph(indptr, indices, train_ids, topk=10):
     R.ref_gc_calculate_color_affinity(h)
     R.ref_gc_destroy(h)
     return color, tk.reshape(nc, topk), sc.reshape(nc, topk)
+
+
+# ---------------------------------------------------------------------------------------------
+# Specification of the GPU mode of the colour-metadata generator (coala_gnn_b200/csrc/coloring_gpu.cu).
+# The reference has no such mode; its own algorithm (M/graph_coloring.cpp) stays pinned by
+# ref_color_graph + tests/golden/coloring_*.npz.  What is restated here is the order-independent
+# definition the kernels implement, in numpy, so the kernels can be checked bit for bit.
+# ---------------------------------------------------------------------------------------------
+def draw_train_seeds(num_nodes, train_ids, base_rate=0.005):
+    """Seeds of cpu_color_graph_optimized (M/graph_coloring.cpp:77-92): glibc rand() stream from seed 1,
+    float(rand()) / RAND_MAX <= base_rate(float) * min(20, N / n_train)(double); train ids are distinct.
+    Returns (nodes, colours)."""
+    libc = C.CDLL("libc.so.6")
+    libc.srand(1)
+    rate = float(np.float32(base_rate)) * min(20.0, float(num_nodes) / float(len(train_ids)))
+    rmax = np.float32(2147483647)
+    nodes = [v for v in _i64a(train_ids).tolist() if float(np.float32(libc.rand()) / rmax) <= rate]
+    nodes = np.array(nodes, dtype=np.int64)
+    return nodes, np.arange(1, len(nodes) + 1, dtype=np.int64)
+
+
+def _expand(indptr, indices, frontier, color):
+    deg = indptr[frontier + 1] - indptr[frontier]
+    if deg.sum() == 0:
+        return np.zeros(0, np.int64), np.zeros(0, np.int64)
+    starts = np.repeat(indptr[frontier], deg)
+    within = np.arange(deg.sum()) - np.repeat(np.cumsum(deg) - deg, deg)
+    return indices[starts + within], np.repeat(color[frontier], deg)
+
+
+def _claim(n, u, c, keep):
+    claim = np.full(n, np.iinfo(np.int64).max, dtype=np.int64)
+    np.minimum.at(claim, u[keep], c[keep])
+    new = np.nonzero(claim != np.iinfo(np.int64).max)[0]
+    return new, claim[new]
+
+
+def levelsync_color_graph(indptr, indices, train_ids, max_hop=10, base_rate=0.005):
+    """Level-synchronous colouring: level 1 = seeds + their uncoloured training in-neighbours, levels
+    2..max_hop = uncoloured in-neighbours of the previous level; the smallest claiming colour wins.
+    Returns (color int64[N], hop uint16[N], num_colors)."""
+    indptr, indices = _i64a(indptr), _i64a(indices)
+    n = len(indptr) - 1
+    is_train = np.zeros(n, dtype=bool)
+    is_train[_i64a(train_ids)] = True
+    seeds, cols = draw_train_seeds(n, train_ids, base_rate)
+    color = np.zeros(n, dtype=np.int64)
+    hop = np.zeros(n, dtype=np.uint16)
+    if max_hop < 1 or len(seeds) == 0:
+        return color, hop, len(seeds)
+    color[seeds] = cols
+    hop[seeds] = 1
+    u, c = _expand(indptr, indices, seeds, color)
+    new, col = _claim(n, u, c, (color[u] == 0) & is_train[u])
+    color[new] = col
+    hop[new] = 1
+    frontier = np.concatenate([seeds, new])
+    for level in range(2, max_hop + 1):
+        u, c = _expand(indptr, indices, frontier, color)
+        new, col = _claim(n, u, c, color[u] == 0)
+        color[new] = col
+        hop[new] = level
+        frontier = new
+    return color, hop, len(seeds)
+
+
+def affinity_from_counts(indptr, indices, color, hop, num_c, topk=10):
+    """score(c, nc) = sum_h count(c, nc, h) * exp(-0.5 h) (ascending h, separately rounded multiply and add),
+    top-k by (score desc, nc asc), divided by the in-edge count of c; colours 1..num_c-1 get a row
+    (loop bound of M/graph_coloring.cpp:266). Returns (topk int64[num_c,K], score float64[num_c,K])."""
+    import math
+    indptr, indices, color = _i64a(indptr), _i64a(indices), _i64a(color)
+    n = len(indptr) - 1
+    deg = np.diff(indptr)
+    v = np.repeat(np.arange(n), deg)
+    c, nc, h = color[v], color[indices], hop[indices].astype(np.int64)
+    ok = (c > 0) & (c < num_c) & (nc != 0) & (nc != c)
+    in_edges = np.bincount(color, weights=deg.astype(np.float64), minlength=num_c + 1)
+    key = (c[ok] << 32) | nc[ok]
+    pairs = np.unique(key)
+    score = np.zeros(len(pairs), dtype=np.float64)
+    for hv in range(16):
+        sel = h[ok] == hv
+        cnt = np.zeros(len(pairs), dtype=np.float64)
+        if sel.any():
+            kk, kc = np.unique(key[sel], return_counts=True)
+            cnt[np.searchsorted(pairs, kk)] = kc
+        score = score + cnt * math.exp(-0.5 * hv)
+    pc, pn = pairs >> 32, pairs & 0xFFFFFFFF
+    order = np.lexsort((pn, -score, pc))
+    tk = np.zeros((num_c, topk), dtype=np.int64)
+    sc = np.zeros((num_c, topk), dtype=np.float64)
+    pc_o, pn_o, s_o = pc[order], pn[order], score[order]
+    first = np.searchsorted(pc_o, np.arange(num_c + 2))
+    for col in range(1, num_c):
+        a, b = first[col], min(first[col + 1], first[col] + topk)
+        tk[col - 1, :b - a] = pn_o[a:b]
+        sc[col - 1, :b - a] = s_o[a:b] / in_edges[col]
+    return tk, sc

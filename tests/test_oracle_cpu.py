@@ -80,6 +80,41 @@ def test_coloring_product_matches_reference_golden(name):
     assert not tk.reshape(nc, 10)[-1].any()  # last colour's row is never filled (reference quirk)
 
 
+@pytest.mark.parametrize("name", ["coloring_2k", "coloring_20k"])
+def test_gpu_mode_affinity_specification_is_pinned_to_the_reference(name):
+    """oracle.affinity_from_counts (the definition the GPU affinity kernels are checked against) on the
+    reference's own colouring reproduces the reference's golden scores to 1e-12 and its top-k lists up to
+    permutations inside tied scores; the level-synchronous colouring draws the reference's seeds."""
+    from coala_gnn_b200.pybind import Graph_Coloring
+    g = _golden(name)
+    n, e, seed = int(g["n"]), int(g["e"]), int(g["seed"])
+    indptr, indices, _ = synth.make_csc(n, e, seed)
+    train = np.arange(int(n * 0.6), dtype=np.int64)
+    ctypes.CDLL("libc.so.6").srand(1)
+    gc = Graph_Coloring(n)
+    gc.set_adj_csc(indptr.ctypes.data, indices.ctypes.data)
+    color = np.zeros(n, dtype=np.int64)
+    gc.set_color_buffer(color.ctypes.data)
+    gc.cpu_color_graph_optimized(train.ctypes.data, len(train))
+    nc = gc.get_num_color()
+    tk, sc = oracle.affinity_from_counts(indptr, indices, color, gc.get_hops(n), nc, 10)
+    assert np.allclose(sc, g["score"], rtol=1e-12, atol=0)
+    r, c = np.nonzero(tk != g["topk"])
+    for i, j in zip(r, c):
+        tied = np.isclose(g["score"][i], g["score"][i, j], rtol=1e-12, atol=0)
+        if not tied[-1]:  # a tie group cut by K may keep different members; its scores are compared above
+            assert sorted(tk[i, tied]) == sorted(g["topk"][i, tied])
+    ls_color, ls_hop, ls_nc = oracle.levelsync_color_graph(indptr, indices, train)
+    assert ls_nc == nc
+    seeds = np.nonzero((ls_hop == 1) & (ls_color != 0))[0]
+    assert set(np.unique(ls_color[ls_color != 0])) <= set(range(1, nc + 1))
+    assert (ls_hop[ls_color != 0] >= 1).all() and ls_hop.max() <= 10 and len(seeds) >= nc
+    # a node coloured at level h > 1 has an in-neighbour... it was claimed FROM a node whose in-neighbour it is
+    for v in np.nonzero(ls_hop > 1)[0][:500]:
+        src = np.nonzero((ls_color == ls_color[v]) & (ls_hop == ls_hop[v] - 1))[0]
+        assert any(v in indices[indptr[s]:indptr[s + 1]] for s in src)
+
+
 # ---------------------------------------------------------------- cache model
 @pytest.mark.parametrize("mode,G", [("isolated", 1), ("partitioned", 4)])
 def test_cache_model_invariants(mode, G):
