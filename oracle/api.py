@@ -121,6 +121,8 @@ class CacheModel:
 
 
 def sample_layer(indptr, indices, edge_ids, seeds, fanout, lkey):
+    if fanout > 64:
+        raise ValueError("oracle sampler: fan-out above MAX_FANOUT (64, oracle/c/sampler.c)")
     indptr, indices, seeds = _i64a(indptr), _i64a(indices), _i64a(seeds)
     edge_ids = _i64a(edge_ids) if edge_ids is not None else None
     deg = indptr[seeds + 1] - indptr[seeds]

@@ -64,7 +64,7 @@ def test_isolated_serial_matches_oracle_exactly(dim):
 
 
 @pytest.mark.parametrize("engine", [0, 1])
-@pytest.mark.parametrize("dim", [128, 1024, 100, 101])
+@pytest.mark.parametrize("dim", [128, 256, 512, 1024, 100, 101])
 def test_isolated_parallel_features_bit_exact_and_invariants(dim, engine):
     """engine 1 = bulk asynchronous copies for hit rows (dim 101 has unaligned rows and must fall back)."""
     from coala_gnn_b200.pybind import Isolated_Cache

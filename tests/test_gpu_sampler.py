@@ -101,3 +101,32 @@ def test_config_shaped_batch_properties():
         assert np.all(pos >= indptr[dst][b.edge_dst.cpu().numpy()]) and np.all(pos < indptr[dst + 1][b.edge_dst.cpu().numpy()])
     einp, _, _ = oracle.sample_blocks_detailed(indptr, indices, None, seeds, [5, 5], oracle.batch_key(1, 0))
     assert np.array_equal(inp_h, einp)
+
+
+def test_degree_boundaries_long_rows_and_empty_batch():
+    """Rows of in-degree 0, 1, fan-out-1, fan-out, fan-out+1, 63, 64, 65 and 200 (the whole-row read covers
+    <= 64 neighbours, longer rows take the per-pick path), the smallest and the largest supported fan-out; a
+    batch of zero seeds; a fan-out above the supported 32 is refused."""
+    import torch
+    from coala_gnn_b200.sampler import MultiLayerNeighborSampler
+    rng = np.random.default_rng(4)
+    n = 3000
+    deg = np.array([0, 1, 4, 5, 6, 63, 64, 65, 200], dtype=np.int64)[np.arange(n) % 9]
+    indptr = np.zeros(n + 1, dtype=np.int64)
+    np.cumsum(deg, out=indptr[1:])
+    indices = rng.integers(0, n, indptr[-1]).astype(np.int64)
+    eids = rng.permutation(indptr[-1]).astype(np.int64)
+    g = _uva_graph(indptr, indices, eids)
+    seeds = rng.permutation(n)[:300].astype(np.int64)
+    for fanouts in ([5, 5], [1, 32], [32, 2]):
+        sampler = MultiLayerNeighborSampler(fanouts, seed=3)
+        for it in range(2):
+            inp, outn, blocks = sampler.sample(g, torch.from_numpy(seeds).cuda())
+            einp, eout, eblocks = oracle.sample_blocks_detailed(indptr, indices, eids, seeds, fanouts, oracle.batch_key(3, it))
+            assert np.array_equal(inp.cpu().numpy(), einp) and np.array_equal(outn.cpu().numpy(), eout)
+            _compare(blocks, eblocks)
+        inp, outn, blocks = sampler.sample(g, torch.zeros(0, dtype=torch.int64, device="cuda"))
+        assert inp.numel() == 0 and outn.numel() == 0
+        assert all(b.num_edges() == 0 and b.number_of_src_nodes() == 0 for b in blocks)
+    with pytest.raises(RuntimeError):
+        MultiLayerNeighborSampler([33]).sample(g, torch.from_numpy(seeds).cuda())
