@@ -20,6 +20,7 @@
 #include "../../include/coala_b200.h"
 #include "coloring.h"
 #include "common.cuh"
+#include <algorithm>
 #include <cmath>
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_run_length_encode.cuh>
@@ -89,13 +90,13 @@ __global__ void gc_commit_kernel(const uint32_t* __restrict__ nodes, uint32_t n,
 
 // warp per node v: in-edge count of its colour, and one key per edge whose far end has another colour
 __global__ void aff_keys_kernel(uint64_t n, const uint64_t* __restrict__ indptr, const uint64_t* __restrict__ indices,
-                                const uint64_t* __restrict__ color, const uint16_t* __restrict__ hop, uint64_t num_c,
-                                unsigned long long* in_edges, uint64_t* keys, unsigned long long* n_keys) {
+                                const uint64_t* __restrict__ color, const uint16_t* __restrict__ hop, uint64_t c_lo, uint64_t c_hi,
+                                unsigned long long* in_edges, uint64_t* keys, unsigned long long cap, unsigned long long* n_keys) {
     const uint64_t v = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const unsigned lane = threadIdx.x & 31;
     if (v >= n) return;
     const uint64_t c = color[v];
-    if (c == 0 || c >= num_c) return;  // the reference's loop stops one colour short (M/graph_coloring.cpp:266)
+    if (c < c_lo || c >= c_hi) return;  // this pass's colour range; c_hi <= num_c: the reference's loop stops one colour short (M/graph_coloring.cpp:266)
     const uint64_t b = indptr[v], e = indptr[v + 1];
     if (lane == 0 && e > b) atomicAdd(&in_edges[c], (unsigned long long)(e - b));
     for (uint64_t k0 = b; k0 < e; k0 += 32) {
@@ -113,7 +114,8 @@ __global__ void aff_keys_kernel(uint64_t n, const uint64_t* __restrict__ indptr,
         unsigned long long base = 0;
         if (lane == 0) base = atomicAdd(n_keys, (unsigned long long)__popc(m));
         base = __shfl_sync(0xffffffffu, base, 0);
-        if (take) keys[base + __popc(m & ((1u << lane) - 1))] = key;
+        const unsigned long long pos = base + __popc(m & ((1u << lane) - 1));
+        if (take && pos < cap) keys[pos] = key;  // an overflowing pass is detected from the counter and refused
     }
 }
 
@@ -144,12 +146,12 @@ __device__ __forceinline__ int64_t lower_bound_key(const uint64_t* a, int64_t n,
 __device__ __forceinline__ bool better(double s1, uint64_t c1, double s2, uint64_t c2) { return s1 > s2 || (s1 == s2 && c1 < c2); }
 
 // warp per colour: k rounds of "best entry that comes after the previous pick"
-__global__ void aff_topk_kernel(uint64_t num_c, int topk, const uint64_t* __restrict__ run_key, const double* __restrict__ pair_score,
+__global__ void aff_topk_kernel(uint64_t c_lo, uint64_t c_hi, int topk, const uint64_t* __restrict__ run_key, const double* __restrict__ pair_score,
                                 const int* __restrict__ n_runs, const unsigned long long* __restrict__ in_edges, uint64_t* topk_color,
                                 double* topk_aff) {
-    const uint64_t c = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) + 1;
+    const uint64_t c = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) + c_lo;
     const unsigned lane = threadIdx.x & 31;
-    if (c >= num_c) return;
+    if (c >= c_hi) return;
     const int64_t n = *n_runs;
     const int64_t lo = lower_bound_key(run_key, n, c << 32), hi = lower_bound_key(run_key, n, (c + 1) << 32);
     double last_s = INFINITY;
@@ -259,59 +261,73 @@ extern "C" int coala_gc_gpu_calculate_color_affinity(coala_gc* g, int device) {
     if (stage_graph(g, device)) return -1;
     const uint64_t n = g->num_nodes, n_edges = g->indptr[n], num_c = g->next_color - 1;
     if (num_c < 2) return 0;
-    if (n_edges >= 0x7FFFFFFFull) COALA_FAIL("Graph_Coloring GPU mode: more than 2^31 edges need a chunked sort (not in this round)");
     const int K = g->topk;
     double h_exp[1 << HOP_BITS];
     for (int h = 0; h < (1 << HOP_BITS); h++) h_exp[h] = std::exp(-0.5 * (double)h);  // score_func (M/graph_coloring.cpp:250-252)
 
-    DevBuf color, hop, in_edges, keys, keys_sorted, n_keys, run_key, run_cnt, n_runs, score, tmp, exp_tab, d_topk, d_aff;
-    const uint64_t cap = n_edges ? n_edges : 1;
+    // The sort runs in passes over disjoint colour ranges so that one pass holds fewer than 2^31 keys (cub's
+    // item counts are int) and at most ~2^30 by default; every pass scans the edges once.  COALA_GC_PARTS forces
+    // the number of passes (tests use it to exercise the multi-pass path on small graphs).
+    uint64_t parts = (n_edges >> 30) + 1;
+    if (const char* e = getenv("COALA_GC_PARTS")) parts = strtoull(e, nullptr, 10) > 0 ? strtoull(e, nullptr, 10) : parts;
+    if (parts > num_c - 1) parts = num_c - 1;
+    // key capacity of a pass: all edges when there is one pass, otherwise twice the even share (colour sizes are skewed)
+    uint64_t cap = n_edges ? n_edges : 1;
+    if (parts > 1) cap = std::min<uint64_t>(cap, 2 * (n_edges / parts) + (1 << 20));
+    if (cap >= 0x7FFFFFFFull) COALA_FAIL("Graph_Coloring GPU mode: a sort pass would exceed 2^31 keys; raise COALA_GC_PARTS");
+
+    DevBuf color, hop, in_edges, keys, keys_sorted, n_keys, run_cnt, n_runs, score, tmp, tmp2, exp_tab, d_topk, d_aff;
     COALA_CUDA(cudaMalloc(&color.p, n * 8));
     COALA_CUDA(cudaMalloc(&hop.p, n * 2));
     COALA_CUDA(cudaMalloc(&in_edges.p, (num_c + 1) * 8));
     COALA_CUDA(cudaMalloc(&keys.p, cap * 8));
     COALA_CUDA(cudaMalloc(&keys_sorted.p, cap * 8));
+    COALA_CUDA(cudaMalloc(&run_cnt.p, cap * 4));
+    COALA_CUDA(cudaMalloc(&score.p, cap * 8));
     COALA_CUDA(cudaMalloc(&n_keys.p, 8));
     COALA_CUDA(cudaMalloc(&n_runs.p, 4));
     COALA_CUDA(cudaMalloc(&exp_tab.p, sizeof(h_exp)));
     COALA_CUDA(cudaMalloc(&d_topk.p, num_c * K * 8));
     COALA_CUDA(cudaMalloc(&d_aff.p, num_c * K * 8));
+    size_t tb = 0, tb2 = 0;  // scratch sized for the largest possible pass
+    COALA_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tb, keys.as<uint64_t>(), keys_sorted.as<uint64_t>(), (int)cap, 0, 32 + COLOR_BITS));
+    COALA_CUDA(cub::DeviceRunLengthEncode::Encode(nullptr, tb2, keys_sorted.as<uint64_t>(), keys.as<uint64_t>(), run_cnt.as<uint32_t>(),
+                                                  n_runs.as<int>(), (int)cap));
+    COALA_CUDA(cudaMalloc(&tmp.p, tb ? tb : 1));
+    COALA_CUDA(cudaMalloc(&tmp2.p, tb2 ? tb2 : 1));
     COALA_CUDA(cudaMemcpy(color.p, g->color, n * 8, cudaMemcpyHostToDevice));
     COALA_CUDA(cudaMemcpy(hop.p, g->hop.data(), n * 2, cudaMemcpyHostToDevice));
     COALA_CUDA(cudaMemset(in_edges.p, 0, (num_c + 1) * 8));
-    COALA_CUDA(cudaMemset(n_keys.p, 0, 8));
     COALA_CUDA(cudaMemcpy(exp_tab.p, h_exp, sizeof(h_exp), cudaMemcpyHostToDevice));
     // rows the kernels do not touch keep the caller's contents, like the reference
     COALA_CUDA(cudaMemcpy(d_topk.p, g->topk_color, num_c * K * 8, cudaMemcpyHostToDevice));
     if (g->topk_aff) COALA_CUDA(cudaMemcpy(d_aff.p, g->topk_aff, num_c * K * 8, cudaMemcpyHostToDevice));
 
-    aff_keys_kernel<<<blocks_for(n * 32, 256), 256>>>(n, g->d_indptr, g->d_indices, color.as<uint64_t>(), hop.as<uint16_t>(), num_c,
-                                                      in_edges.as<unsigned long long>(), keys.as<uint64_t>(), n_keys.as<unsigned long long>());
-    unsigned long long nk = 0;
-    COALA_CUDA(cudaMemcpy(&nk, n_keys.p, 8, cudaMemcpyDeviceToHost));
-    if (nk) {
-        size_t tb = 0;
-        COALA_CUDA(cub::DeviceRadixSort::SortKeys(nullptr, tb, keys.as<uint64_t>(), keys_sorted.as<uint64_t>(), (int)nk, 0, 32 + COLOR_BITS));
-        COALA_CUDA(cudaMalloc(&tmp.p, tb ? tb : 1));
-        COALA_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, tb, keys.as<uint64_t>(), keys_sorted.as<uint64_t>(), (int)nk, 0, 32 + COLOR_BITS));
-        // the unsorted key buffer is free again: reuse it for the run keys; counts and scores get their own
-        COALA_CUDA(cudaMalloc(&run_cnt.p, nk * 4));
-        COALA_CUDA(cudaMalloc(&score.p, nk * 8));
-        size_t tb2 = 0;
-        COALA_CUDA(cub::DeviceRunLengthEncode::Encode(nullptr, tb2, keys_sorted.as<uint64_t>(), keys.as<uint64_t>(), run_cnt.as<uint32_t>(),
-                                                      n_runs.as<int>(), (int)nk));
-        DevBuf tmp2;
-        COALA_CUDA(cudaMalloc(&tmp2.p, tb2 ? tb2 : 1));
-        COALA_CUDA(cub::DeviceRunLengthEncode::Encode(tmp2.p, tb2, keys_sorted.as<uint64_t>(), keys.as<uint64_t>(), run_cnt.as<uint32_t>(),
+    for (uint64_t part = 0; part < parts; part++) {
+        // colours 1 .. num_c-1 split evenly
+        const uint64_t c_lo = 1 + (num_c - 1) * part / parts, c_hi = 1 + (num_c - 1) * (part + 1) / parts;
+        if (c_hi <= c_lo) continue;
+        COALA_CUDA(cudaMemset(n_keys.p, 0, 8));
+        aff_keys_kernel<<<blocks_for(n * 32, 256), 256>>>(n, g->d_indptr, g->d_indices, color.as<uint64_t>(), hop.as<uint16_t>(), c_lo, c_hi,
+                                                          in_edges.as<unsigned long long>(), keys.as<uint64_t>(), cap,
+                                                          n_keys.as<unsigned long long>());
+        unsigned long long nk = 0;
+        COALA_CUDA(cudaMemcpy(&nk, n_keys.p, 8, cudaMemcpyDeviceToHost));
+        if (nk > cap) COALA_FAIL("Graph_Coloring GPU mode: a colour range holds more edges than a sort pass; raise COALA_GC_PARTS");
+        if (nk == 0) continue;
+        size_t t1 = tb, t2 = tb2;
+        COALA_CUDA(cub::DeviceRadixSort::SortKeys(tmp.p, t1, keys.as<uint64_t>(), keys_sorted.as<uint64_t>(), (int)nk, 0, 32 + COLOR_BITS));
+        // the unsorted key buffer is free again: it receives the run keys
+        COALA_CUDA(cub::DeviceRunLengthEncode::Encode(tmp2.p, t2, keys_sorted.as<uint64_t>(), keys.as<uint64_t>(), run_cnt.as<uint32_t>(),
                                                       n_runs.as<int>(), (int)nk));
         aff_pair_kernel<<<blocks_for(nk, 256), 256>>>(keys.as<uint64_t>(), run_cnt.as<uint32_t>(), n_runs.as<int>(), exp_tab.as<double>(),
                                                       score.as<double>());
-        aff_topk_kernel<<<blocks_for((num_c - 1) * 32, 256), 256>>>(num_c, K, keys.as<uint64_t>(), score.as<double>(), n_runs.as<int>(),
-                                                                    in_edges.as<unsigned long long>(), d_topk.as<uint64_t>(),
-                                                                    g->topk_aff ? d_aff.as<double>() : nullptr);
+        aff_topk_kernel<<<blocks_for((c_hi - c_lo) * 32, 256), 256>>>(c_lo, c_hi, K, keys.as<uint64_t>(), score.as<double>(), n_runs.as<int>(),
+                                                                      in_edges.as<unsigned long long>(), d_topk.as<uint64_t>(),
+                                                                      g->topk_aff ? d_aff.as<double>() : nullptr);
         COALA_CUDA(cudaGetLastError());
-        COALA_CUDA(cudaDeviceSynchronize());
     }
+    COALA_CUDA(cudaDeviceSynchronize());
     COALA_CUDA(cudaMemcpy(g->topk_color, d_topk.p, num_c * K * 8, cudaMemcpyDeviceToHost));
     if (g->topk_aff) COALA_CUDA(cudaMemcpy(g->topk_aff, d_aff.p, num_c * K * 8, cudaMemcpyDeviceToHost));
     return 0;

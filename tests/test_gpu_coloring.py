@@ -67,8 +67,13 @@ def test_gpu_colouring_matches_levelsync_specification(name):
     assert not tk[-1].any()  # the last colour's row stays empty, like the reference
 
 
+@pytest.mark.parametrize("parts", [None, "3", "1000000"])
 @pytest.mark.parametrize("name", ["coloring_2k", "coloring_20k"])
-def test_gpu_affinity_on_reference_colouring(name):
+def test_gpu_affinity_on_reference_colouring(name, parts, monkeypatch):
+    """parts: the sort runs in that many passes over disjoint colour ranges (graphs above 2^30 edges do that on
+    their own; forced here on small graphs, "1000000" = one colour per pass)."""
+    if parts:
+        monkeypatch.setenv("COALA_GC_PARTS", parts)
     g, n, indptr, indices, train = _graph(name)
     gc, color = _new_gc(n, indptr, indices)
     gc.cpu_color_graph_optimized(train.ctypes.data, len(train))  # host mode == reference (pinned by the golden fixture)
