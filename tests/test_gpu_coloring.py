@@ -119,3 +119,25 @@ def test_gpu_colour_metadata_feeds_the_distributor():
         assert np.array_equal(out, exp)
         outs.append(out)
     assert np.array_equal(np.sort(np.concatenate(outs)), np.sort(items[:D * L * B]))
+
+
+def test_generate_color_data_script_gpu_mode(tmp_path):
+    """examples/generate_color_data.py --mode gpu over the on-disk CSC layout: files equal the specification's arrays."""
+    import importlib.util
+    import os
+    g, n, indptr, indices, train = _graph("coloring_2k")
+    cites = os.path.join(str(tmp_path), "tiny", "processed", "paper__cites__paper")
+    os.makedirs(cites)
+    np.save(os.path.join(cites, "csc_indptr.npy"), indptr)
+    np.save(os.path.join(cites, "csc_indices.npy"), indices)
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    spec = importlib.util.spec_from_file_location("generate_color_data", os.path.join(root, "examples", "generate_color_data.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    out = os.path.join(str(tmp_path), "meta")
+    mod.main(["--path", str(tmp_path), "--dataset_size", "tiny", "--mode", "gpu", "--out_path", out])
+    exp_color, exp_hop, exp_nc = oracle.levelsync_color_graph(indptr, indices, train)
+    etk, esc = oracle.affinity_from_counts(indptr, indices, exp_color, exp_hop, exp_nc, K)
+    assert np.array_equal(np.load(os.path.join(out, "color.npy")), exp_color)
+    assert np.array_equal(np.load(os.path.join(out, "topk.npy")), etk)
+    assert np.array_equal(np.load(os.path.join(out, "score.npy")).view(np.uint64), esc.view(np.uint64))

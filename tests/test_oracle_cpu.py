@@ -211,3 +211,29 @@ def test_npy_streaming_copy_pads_rows(tmp_path):
     assert np.array_equal(d1, v)
     with pytest.raises(ValueError):
         _copy_npy_into(np.empty(10, dtype=np.int64), p)
+
+
+def _write_csc_layout(root, name):
+    g = _golden(name)
+    n, e, seed = int(g["n"]), int(g["e"]), int(g["seed"])
+    indptr, indices, _ = synth.make_csc(n, e, seed)
+    cites = os.path.join(root, "tiny", "processed", "paper__cites__paper")
+    os.makedirs(cites)
+    np.save(os.path.join(cites, "csc_indptr.npy"), indptr)
+    np.save(os.path.join(cites, "csc_indices.npy"), indices)
+    return g, indptr, indices
+
+
+def test_generate_color_data_script_host_mode_writes_reference_files(tmp_path):
+    """examples/generate_color_data.py (counterpart of the reference's color_info_gen script) in host mode
+    writes exactly the arrays the reference's Graph_Coloring produced for the golden fixture."""
+    import importlib.util
+    g, _, _ = _write_csc_layout(str(tmp_path), "coloring_2k")
+    spec = importlib.util.spec_from_file_location("generate_color_data", os.path.join(ROOT, "examples", "generate_color_data.py"))
+    mod = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(mod)
+    mod.main(["--path", str(tmp_path), "--dataset_size", "tiny", "--mode", "host"])
+    out = os.path.join(str(tmp_path), "tiny")
+    assert np.array_equal(np.load(os.path.join(out, "color.npy")), g["color"])
+    assert np.array_equal(np.load(os.path.join(out, "topk.npy")), g["topk"])
+    assert np.array_equal(np.load(os.path.join(out, "score.npy")).view(np.uint64), g["score"].view(np.uint64))
