@@ -131,7 +131,7 @@ def build_world(args):
     fan = [int(f) for f in args.fan_out.split(",")]
     train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=0))
     nd = Node_Distributor(comm, train, args.batch_size, ds.color_file, ds.topk_file, ds.score_file, parsing_method=args.distribution)
-    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank, hbm_indptr=args.hbm_indptr)
+    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank, hbm_indptr=True if args.hbm_indptr else None)
     backend = args.cache_backend
     loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, sampler, args.batch_size, ds.dim, fan,
                                   args.cache_size, device, refresh_counter=args.refresh_counter, cache_backend=backend,
@@ -357,7 +357,7 @@ def run_ours(args):
                        % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, B, args.cache_size, args.cache_backend, comm.num_master_process, L, args.distribution),
                        "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (a different row set every step; the table is %.0f GB, L2 is 126 MB)" % (rows * R / 1e6, ds.num_nodes * R / 1e9),
                        "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter,
-                       "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr copy in HBM" if args.hbm_indptr else "")},
+                       "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr copy in HBM" if sampler.hbm_indptr else "")},
             "hit_ratio": hs / max(1.0, hs + ms_ + bs), "rows_per_step": rows,
             "gather_GBs": rows * R / t_meas / 1e9, "sample_stream_ms": sample_ms,
             # the dominant kernel against the link that bounds it (T_bound = max over links of bytes/peak);
