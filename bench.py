@@ -265,11 +265,15 @@ def run_ours(args):
     rh, rm, rb = cache.stats(reset=True)
     # the same lists once more with copy engine 1 (hit rows as bulk asynchronous copies through shared memory); the 7 other
     # lists (~0.7 GB) have passed through L2 since a list was last touched
-    replay_e1_ms, replay_e1_err = None, None
+    replay_e1_ms, replay_e1_err = None, "not run (multi-process runs only with COALA_BENCH_REPLAY_ENGINE1=1)"
     try:
-        cache.set_copy_engine(1)
+        # engine 1 over peer mappings has been measured in-process (scripts/bench_gather.py --gpus 2), not yet across
+        # processes: a device fault there could not be caught, so multi-rank runs keep to engine 0 unless asked
         r = []
-        for ids in lists:
+        use_e1 = N == 1 or os.environ.get("COALA_BENCH_REPLAY_ENGINE1") == "1"
+        if use_e1:
+            cache.set_copy_engine(1)
+        for ids in (lists if use_e1 else []):
             barrier_sync(comm)
             r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             r0.record()
@@ -277,7 +281,8 @@ def run_ours(args):
             r1.record()
             torch.cuda.synchronize()
             r.append(r0.elapsed_time(r1))
-        replay_e1_ms = float(np.median(r))
+        if r:
+            replay_e1_ms = float(np.median(r))
     except RuntimeError as e:  # symmetric on all ranks (same launch, same arguments): the barriers stay matched
         replay_e1_err = str(e)
     finally:
