@@ -65,8 +65,15 @@ class SyntheticSharedCSCUVA(object):
         self.meta_dir = os.path.join(tempfile.gettempdir(), "coala_b200_%s_meta" % tag)
         if rank0:
             os.makedirs(self.meta_dir, exist_ok=True)
-            C = num_colors or max(16, int(0.005 * n))
-            color, topk, score = synth.block_color_meta(n, C)
+            # COALA_SYNTH_COLOR = block (default: id-block stand-in) | graph (the reference's colouring, host mode,
+            # ~15 s at 10 M nodes) | graph_gpu (same seeds, GPU mode, ~0.3 s) - SURVEY 8(d) "colour metadata for each
+            # graph comes from the colouring with the reference call order"
+            how = os.environ.get("COALA_SYNTH_COLOR", "block")
+            if how == "block":
+                C = num_colors or max(16, int(0.005 * n))
+                color, topk, score = synth.block_color_meta(n, C)
+            else:
+                color, topk, score = _graph_color_meta(self.csc_host[0], self.csc_host[1], n, how == "graph_gpu", comm_manager.device_index)
             np.save(os.path.join(self.meta_dir, "color.npy"), color)
             np.save(os.path.join(self.meta_dir, "topk.npy"), topk)
             np.save(os.path.join(self.meta_dir, "score.npy"), score)
@@ -109,6 +116,31 @@ def _copy_npy_into(dst, path, threads=8, chunk_rows=None):
             dst[lo:hi] = src[lo:hi]
     with ThreadPoolExecutor(max_workers=threads) as ex:
         list(ex.map(work, range(0, n, chunk_rows)))
+
+
+def _graph_color_meta(indptr, indices, n, gpu, device_index):
+    """Graph_Coloring in the call order of examples/color_info_gen/generate_color_data.py:20-54 (reference)."""
+    import ctypes
+    from .pybind import Graph_Coloring
+    train = np.arange(int(n * 0.6), dtype=np.int64)
+    ctypes.CDLL("libc.so.6").srand(1)  # the reference never seeds rand()
+    tool = Graph_Coloring(n)
+    tool.set_adj_csc(indptr.ctypes.data, indices.ctypes.data)
+    color = np.zeros(n, dtype=np.int64)
+    tool.set_color_buffer(color.ctypes.data)
+    if gpu:
+        tool.gpu_color_graph_optimized(train.ctypes.data, len(train), device_index)
+    else:
+        tool.cpu_color_graph_optimized(train.ctypes.data, len(train))
+    nc = tool.get_num_color()
+    topk, score = np.zeros(nc * 10, dtype=np.int64), np.zeros(nc * 10, dtype=np.float64)
+    tool.set_topk_color_buffer(topk.ctypes.data)
+    tool.set_topk_affinity_buffer(score.ctypes.data)
+    if gpu:
+        tool.gpu_calculate_color_affinity(device_index)
+    else:
+        tool.cpu_calculate_color_affinity()
+    return color, topk.reshape(nc, 10), score.reshape(nc, 10)
 
 
 def npy_shape(path):

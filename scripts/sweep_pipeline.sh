@@ -26,6 +26,7 @@ run COALA_HBM_INDPTR=1 COALA_GATHER_ENGINE=1
 run COALA_PREFETCH_DEPTH=2
 run COALA_PREFETCH_DEPTH=4
 run COALA_GATHER_CTAS_PER_SM=1
+run COALA_SYNTH_COLOR=graph_gpu
 python - "$out" <<'PY'
 import json, sys
 label = None
