@@ -6,14 +6,22 @@
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One JSON line on rank 0.  A "step" is one mini-batch (batch 1024, SAGE fan-out 5,5) per GPU.
-  value : device-resident pipeline (coala_gnn_b200.pipeline.DevicePipeline), CUDA-event timed;
-  e2e   : the drop-in COALA_GNN_DataLoader iterator with host seed lists / host metadata;
+  value    : device-resident pipeline (coala_gnn_b200.pipeline.DevicePipeline), CUDA-event timed in steady state:
+             K-step windows recorded back to back (no drain in between) for >= --min_seconds, bracketed by
+             barrier + synchronize, max over ranks per window, the MEDIAN window is reported;
+  e2e      : the drop-in COALA_GNN_DataLoader iterator with host seed lists / host metadata (same windows, host clock);
+  parity   : after each timed leg the next K batches of EVERY rank are checked bit for bit: gathered rows against
+             the procedural feature table, sampled blocks (and the seed distribution) against the CPU oracle;
   roofline : the gather kernel, timed live with CUDA events inside the timed region;
-  cpu_baseline : oracle sampler (OpenMP) + index_select on the host cores (bounded sample).
-`--impl reference` times that CPU path as its own arm.
+  cpu_baseline : oracle sampler (OpenMP) + torch.index_select on the host cores (bounded sample);
+  extras   : the same path in the other regimes of the reference's experiment matrix (whole table resident,
+             node_color vs baseline over D x L cache domains, cache backends), each warmed and timed the same way.
+`--impl reference` times the CPU path as its own arm.
 """
 import argparse
+import ctypes as C
 import json
+import math
 import os
 import subprocess
 import sys
@@ -26,25 +34,32 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
 METRIC = "mini-batches/s (IGB-medium-shaped synthetic graph, SAGE fan-out 5,5, batch 1024 per GPU; seed distribution + UVA sampling + cached feature gather)"
+NVL_PEAK = 770.0  # GB/s per direction: the measured peer-copy figure of B200_PROFILING.md (900 nominal); scripts/bench_gather.py reads 777 with a kernel
 
 
 def parse_args():
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
-    p.add_argument("--steps", type=int, default=500)
+    p.add_argument("--steps", type=int, default=100)
     p.add_argument("--warmup", type=int, default=20)
     p.add_argument("--impl", default="ours", choices=["ours", "reference"])
     p.add_argument("--shape", default=os.environ.get("COALA_BENCH_SHAPE", "igb-medium"))
     p.add_argument("--cache_size", type=int, default=16384, help="MB per GPU (reference flag name)")
     p.add_argument("--cache_backend", default="nvshmem", choices=["nvshmem", "p2p", "isolated", "nccl"])
     p.add_argument("--distribution", default="node_color", choices=["node_color", "baseline"])
+    p.add_argument("--gpus_per_domain", type=int, default=0, help="L: GPUs sharing one partitioned cache (0 = all: one 1xN domain); "
+                                                                  "D = N / L cache domains stand in for the reference's machines (SLURM_NODEID)")
     p.add_argument("--batch_size", type=int, default=1024)
     p.add_argument("--fan_out", default="5,5")
     p.add_argument("--refresh_counter", type=int, default=10)
-    p.add_argument("--prewarm", type=int, default=-1, help="untimed batches that warm the cache (-1: one pass budgeted by --prewarm_seconds)")
+    p.add_argument("--prewarm", type=int, default=-1, help="untimed batches that warm the cache (-1: budgeted by --prewarm_seconds)")
     p.add_argument("--prewarm_seconds", type=float, default=25.0)
+    p.add_argument("--min_seconds", type=float, default=2.0, help="timed windows of --steps are repeated until they cover this long")
     p.add_argument("--cpu_baseline_seconds", type=float, default=12.0)
     p.add_argument("--no_cpu_baseline", action="store_true")
+    p.add_argument("--extras", default=os.environ.get("COALA_BENCH_EXTRAS", "auto"),
+                   help="auto | none | comma list of all_resident,distribution,backends")
+    p.add_argument("--extras_budget", type=float, default=300.0, help="seconds after which the extras are abandoned and the main line printed")
     p.add_argument("--hbm_indptr", action="store_true", help="B200 option: sampler keeps a copy of indptr (80 MB) in HBM")
     p.add_argument("--no_prefetch", action="store_true", help="diagnostic: sample and gather of a batch back to back, no batch in flight")
     p.add_argument("--profile_e2e", action="store_true", help="cProfile the host side of the e2e loop (rank 0) to stderr")
@@ -54,7 +69,8 @@ def parse_args():
 
 
 class ClockSampler(object):
-    """nvidia-smi clocks + throttle reasons during the timed region (B200_PROFILING.md recipe)."""
+    """nvidia-smi clocks + throttle reasons (B200_PROFILING.md recipe), sampled from process start; stop(t0, t1)
+    keeps the samples that fall inside the timed region."""
     Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
 
     def __init__(self, index=0):
@@ -69,33 +85,39 @@ class ClockSampler(object):
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([x.strip() for x in line.split(",")])
+            self.rows.append((time.time(), [x.strip() for x in line.split(",")]))
 
-    def stop(self):
+    def stop(self, regions):
         if not self.proc:
-            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"], "samples": 0}
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        rows = [r for ts, r in self.rows if len(r) >= 7 and any(a <= ts <= b + 0.1 for a, b in regions)]
+        sm = [float(r[0]) for r in rows if r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(r) >= 7 and r[3 + i].lower().startswith("active") for r in self.rows)]
+        reasons = [n for i, n in enumerate(names) if any(r[3 + i].lower().startswith("active") for r in rows)]
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
-                "samples": len(sm)}
+                "samples": len(sm), "samples_whole_run": len(self.rows)}
 
 
 def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads=None):
-    """The reference's CPU formulation of the path (BASELINE.json: "DGL CPU sampler + torch index_select
-    gather"): oracle OpenMP sampler + to_block, then a row gather from the host feature table."""
+    """The reference's CPU formulation of the path (BASELINE.json: "DGL CPU sampler + torch index_select gather"):
+    the oracle's OpenMP restatement of the DGL CPU sampler + to_block (DGL is absent from the image), then
+    torch.index_select on the host feature table with all host threads."""
     import oracle
+    import torch
     indptr, indices, feat = ds_host
     threads = threads or os.cpu_count()
+    torch.set_num_threads(threads)
+    feat_t = torch.from_numpy(feat)
     max_sample = B
     for f in fan:
         max_sample *= f + 1
+    out = torch.empty((max_sample, feat.shape[1]), dtype=torch.float32)
     times, rows = [], 0
     i = 0
     t_end = time.time() + seconds if seconds else None
@@ -103,7 +125,7 @@ def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads
         seeds = train[(i % (len(train) // B - 1)) * B:][:B]
         t0 = time.perf_counter()
         inp, _ = oracle.sample_blocks_fast(indptr, indices, seeds, fan, oracle.batch_key(1, i), max_sample, threads)
-        out = oracle.index_select(feat, inp, threads)
+        torch.index_select(feat_t, 0, torch.from_numpy(inp), out=out[:len(inp)])
         dt = time.perf_counter() - t0
         if i >= warmup:
             times.append(dt)
@@ -113,32 +135,14 @@ def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads
             break
         if t_end is not None and time.time() > t_end and len(times) >= 3:
             break
-    del out
     tot = float(np.sum(times))
     return {"batches_per_s": len(times) / tot, "ms_per_step": 1e3 * tot / len(times), "rows_per_step": rows / len(times),
             "gather_GBs": rows * feat.shape[1] * 4 / tot / 1e9, "steps": len(times), "threads": threads}
 
 
-def build_world(args):
-    import torch
-    from COALA_GNN import MPI_Comm_Manager, Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
-    from coala_gnn_b200.datasets import SyntheticSharedCSCUVA
-    from coala_gnn_b200 import synth
-    comm = MPI_Comm_Manager(-1)  # one cache domain spanning all ranks of the box
-    torch.cuda.set_device(comm.device_index)
-    device = "cuda:%d" % comm.device_index
-    ds = SyntheticSharedCSCUVA(args.shape, comm, device, verbose=True)
-    fan = [int(f) for f in args.fan_out.split(",")]
-    train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=0))
-    nd = Node_Distributor(comm, train, args.batch_size, ds.color_file, ds.topk_file, ds.score_file, parsing_method=args.distribution)
-    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank, hbm_indptr=True if args.hbm_indptr else None)
-    backend = args.cache_backend
-    loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, sampler, args.batch_size, ds.dim, fan,
-                                  args.cache_size, device, refresh_counter=args.refresh_counter, cache_backend=backend,
-                                  sim_buf=ds.feat_data)
-    return comm, ds, train, fan, nd, sampler, loader, device
-
-
+# ------------------------------------------------------------------------------------------------------------
+# helpers shared by every leg
+# ------------------------------------------------------------------------------------------------------------
 def barrier_sync(comm):
     import torch
     import torch.distributed as dist
@@ -148,94 +152,218 @@ def barrier_sync(comm):
     torch.cuda.synchronize()
 
 
-def max_over_ranks(comm, x, device):
+def reduce_ranks(comm, xs, device, op="sum"):
     import torch
     import torch.distributed as dist
+    xs = [float(x) for x in xs]
     if comm.global_size == 1:
-        return x
-    t = torch.tensor([x], dtype=torch.float64, device=device)
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    return float(t.item())
-
-
-def sum_over_ranks(comm, xs, device):
-    import torch
-    import torch.distributed as dist
-    if comm.global_size == 1:
-        return list(xs)
-    t = torch.tensor(list(xs), dtype=torch.float64, device=device)
-    dist.all_reduce(t, op=dist.ReduceOp.SUM)
+        return xs
+    t = torch.tensor(xs, dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX if op == "max" else dist.ReduceOp.SUM)
     return [float(v) for v in t.tolist()]
 
 
-def run_ours(args):
-    import ctypes as C
+def n_windows_for(comm, rate_per_rank, K, min_seconds, device):
+    """How many K-step windows cover min_seconds at the observed rate; the same number on every rank."""
+    n = int(math.ceil(min_seconds * max(rate_per_rank, 1.0) / K))
+    n = max(3, min(n, 4000))
+    return int(reduce_ranks(comm, [n], device, "max")[0])
+
+
+def timed_windows(comm, step_fn, K, n_windows, refill, device, profiler_range=False):
+    """Steady-state timing.  barrier + synchronize; `refill` untimed steps (the synchronize completed every prefetched
+    batch: without them the first `depth` timed steps would be free); then n_windows windows of exactly K steps each,
+    one CUDA event between windows on the consumer stream and NO synchronisation in between; barrier + synchronize.
+    Returns (per-window ms as the max over ranks, host time stamps of the region)."""
+    import torch
+    barrier_sync(comm)
+    for _ in range(refill):
+        step_fn()
+    evs = [torch.cuda.Event(enable_timing=True) for _ in range(n_windows + 1)]
+    if profiler_range:
+        torch.cuda.profiler.start()
+    t_a = time.time()
+    evs[0].record()
+    for w in range(n_windows):
+        for _ in range(K):
+            step_fn()
+        evs[w + 1].record()
+    torch.cuda.synchronize()
+    if profiler_range:
+        torch.cuda.profiler.stop()
+    t_b = time.time()
+    barrier_sync(comm)
+    ms = [evs[i].elapsed_time(evs[i + 1]) for i in range(n_windows)]
+    return reduce_ranks(comm, ms, device, "max"), (t_a, t_b)
+
+
+def build_world(args, comm=None, ds=None, cache_size=None, backend=None, distribution=None, gpus_per_domain=None):
+    """Comm manager (D x L domains), synthetic dataset, distributor, sampler, drop-in loader."""
+    import torch
+    from COALA_GNN import MPI_Comm_Manager, Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
+    from coala_gnn_b200.datasets import SyntheticSharedCSCUVA
+    from coala_gnn_b200 import synth
+    if comm is None:
+        L = gpus_per_domain if gpus_per_domain is not None else args.gpus_per_domain
+        comm = MPI_Comm_Manager(-1, gpus_per_domain=L if L else None)  # default: one cache domain spanning all ranks of the box
+    torch.cuda.set_device(comm.device_index)
+    device = "cuda:%d" % comm.device_index
+    if ds is None:
+        ds = SyntheticSharedCSCUVA(args.shape, comm, device, verbose=True)
+    fan = [int(f) for f in args.fan_out.split(",")]
+    train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=0))
+    nd = Node_Distributor(comm, train, args.batch_size, ds.color_file, ds.topk_file, ds.score_file,
+                          parsing_method=distribution or args.distribution)
+    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank, hbm_indptr=True if args.hbm_indptr else None)
+    loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, sampler, args.batch_size, ds.dim, fan,
+                                  cache_size or args.cache_size, device, refresh_counter=args.refresh_counter,
+                                  cache_backend=backend or args.cache_backend, sim_buf=ds.feat_data)
+    loader.COALA_GNN_Manager.COALA_GNN_Cache.set_num_nodes(ds.num_nodes)
+    return comm, ds, train, fan, nd, sampler, loader, device
+
+
+class Checker(object):
+    """Bitwise parity of what a leg produced, on this rank: gathered rows against the procedural feature table
+    (re-derived on the GPU, coala_synth_check_rows — the reference's own invariant feat[i] == table[input_nodes[i]],
+    examples/nvshmem_homogeneous_train.py:186-198), sampled blocks and the seed distribution against the CPU oracle."""
+
+    def __init__(self, comm, ds, train, fan, nd, device):
+        import oracle
+        self.oracle = oracle
+        self.comm, self.ds, self.fan, self.nd, self.device = comm, ds, fan, nd, device
+        self.train = train.numpy()
+        self.tot = dict(batches=0, rows_checked=0, mismatches=0, blocks_checked=0, block_mismatches=0, seed_lists_checked=0,
+                        seed_mismatches=0, refused_ids=0)
+        self._tables = None
+
+    def rows(self, feat_ptr, idx_ptr, n):
+        from coala_gnn_b200._lib import lib, check
+        bad = C.c_int64()
+        check(lib().coala_synth_check_rows(int(feat_ptr), int(idx_ptr), int(n), self.ds.dim, self.ds.dim, self.ds.feat_seed, C.byref(bad)))
+        self.tot["batches"] += 1
+        self.tot["rows_checked"] += int(n)
+        self.tot["mismatches"] += int(bad.value)
+
+    def blocks(self, seeds_h, key, input_nodes_h, edge_src_h):
+        indptr, indices, _ = self.ds.csc_host
+        einp, _, eblocks = self.oracle.sample_blocks_detailed(indptr, indices, None, seeds_h, self.fan, key)
+        ok = np.array_equal(input_nodes_h, einp) and np.array_equal(edge_src_h, eblocks[0]["edge_src"])
+        self.tot["blocks_checked"] += 1
+        self.tot["block_mismatches"] += 0 if ok else 1
+
+    def seeds(self, seeds_h, offset, metas_h, method):
+        """this rank's B seeds of the step whose global slice starts at `offset`"""
+        comm, B = self.comm, self.nd.batch_size
+        L, D = comm.local_size, comm.num_master_process
+        if method == "baseline" or D == 1:
+            lo = offset + (comm.master_process_index * B * L if method == "baseline" else 0) + comm.local_rank * B
+            exp = self.train[lo:lo + B]
+        else:
+            if self._tables is None:
+                self._tables = tuple(np.load(f) for f in (self.ds.color_file, self.ds.topk_file, self.ds.score_file))
+            color, topk, score = self._tables
+            dom, _ = self.oracle.distribute(self.train, offset, comm.master_process_index, B, L, D, color, topk, score, list(metas_h))
+            exp = dom[comm.local_rank * B:(comm.local_rank + 1) * B]
+        self.tot["seed_lists_checked"] += 1
+        self.tot["seed_mismatches"] += 0 if np.array_equal(seeds_h, exp) else 1
+
+    def summary(self):
+        keys = sorted(self.tot)
+        vals = reduce_ranks(self.comm, [self.tot[k] for k in keys], self.device)
+        out = {k: int(v) for k, v in zip(keys, vals)}
+        out["ranks"] = self.comm.global_size
+        out["ok"] = out["mismatches"] == 0 and out["block_mismatches"] == 0 and out["seed_mismatches"] == 0 and out["refused_ids"] == 0
+        return out
+
+
+def check_pipeline(pipe, chk, K, oracle_batches=4):
+    """The next K batches of the device-resident pipeline, checked one by one (untimed)."""
     import torch
     from coala_gnn_b200._lib import lib, check
-    from coala_gnn_b200.pipeline import DevicePipeline
-    comm, ds, train, fan, nd, sampler, loader, device = build_world(args)
-    N, B, R = comm.global_size, args.batch_size, ds.cache_dim * 4
-    cache = loader.COALA_GNN_Manager.COALA_GNN_Cache
-    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
-    hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
-    if os.path.exists(peaks_path):
-        hbm_peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json"
-    gb = C.c_double()
-    check(lib().coala_probe_read_bandwidth(ds.feat_data.data_ptr(), min(ds.num_nodes * R, 4 << 30), 2, C.byref(gb)))
-    host_peak = gb.value
-
-    pipe = DevicePipeline(loader, record_gather_events=True, seed=1001, prefetch=not args.no_prefetch)  # its own sample stream: the e2e leg must not replay these batches
-    spe = pipe.steps_per_epoch()
-
-    def pipe_steps(n):
-        for _ in range(n):
-            pipe.step()  # epochs wrap inside the pipeline
-
-    # ---- untimed cache pre-warm through the real path (steady state is what an epoch sees)
-    t0 = time.time()
-    n_pre = 0
-    budget = args.prewarm if args.prewarm >= 0 else 10 ** 9
-    while n_pre < budget:
-        pipe_steps(50)
+    from coala_gnn_b200.pybind import tensor_from_ptr
+    from coala_gnn_b200.sampler import batch_key
+    L = len(chk.fan)
+    for i in range(K):
+        out = pipe.step()
         torch.cuda.synchronize()
-        n_pre += 50
-        if args.prewarm < 0:  # every rank must leave after the same batch (the path holds collectives)
-            if max_over_ranks(comm, float(time.time() - t0 > args.prewarm_seconds), device) > 0:
-                break
-    pre_stats = cache.stats(reset=True)
-    pipe.engine.gather_times.clear()
-    pipe.engine.sample_times.clear()
+        t = pipe.step_idx - 1
+        sl = pipe.engine.slot_of(t)
+        cnts = (C.c_int64 * (2 * L + 1))()
+        check(lib().coala_sampler_counts(sl.sampler._h, cnts))
+        n = int(cnts[0])
+        idx_ptr, _ = sl.sampler.input_nodes_dev_ptrs()
+        chk.rows(out.data_ptr(), idx_ptr, n)
+        if i < oracle_batches:
+            seeds_h = sl.last_seeds.cpu().numpy()
+            inp = tensor_from_ptr(idx_ptr, (n,), torch.int64, chk.device).cpu().numpy()
+            es = C.c_uint64()
+            check(lib().coala_sampler_layer_ptrs(sl.sampler._h, 0, None, C.byref(es), None, None))
+            edge_src = tensor_from_ptr(es.value, (int(cnts[1]),), torch.int64, chk.device).cpu().numpy()
+            chk.blocks(seeds_h, batch_key(pipe.engine.seed, t, pipe.engine.rank), inp, edge_src)
+            chk.seeds(seeds_h, pipe.seed_offset(t), sl.meta_used.cpu().numpy(), pipe.nd.parsing_method)
+    chk.tot["refused_ids"] += pipe.mgr.COALA_GNN_Cache.refused_ids()
 
-    # ---- value: device-resident pipeline
-    pipe_steps(args.warmup)
-    barrier_sync(comm)
+
+def measure_pipeline(args, comm, loader, device, K, min_seconds, rate_hint, warmup, seed=1001, profiler_range=False):
+    """value-style measurement of one configured loader through DevicePipeline.  Returns (pipe, result dict)."""
+    import torch
+    from coala_gnn_b200.pipeline import DevicePipeline
+    cache = loader.COALA_GNN_Manager.COALA_GNN_Cache
+    pipe = DevicePipeline(loader, record_gather_events=True, seed=seed, prefetch=not args.no_prefetch)
+    for _ in range(warmup):
+        pipe.step()
+    nw = n_windows_for(comm, rate_hint, K, min_seconds, device)
+    torch.cuda.synchronize()
     cache.stats(reset=True)
     pipe.engine.gather_times.clear()
     pipe.engine.sample_times.clear()
-    clocks = ClockSampler(comm.device_index) if comm.global_rank == 0 else None
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    if args.cuda_profiler_range:
-        torch.cuda.profiler.start()
-    e0.record()
-    pipe_steps(args.steps)
-    e1.record()
-    if args.cuda_profiler_range:
-        torch.cuda.synchronize()
-        torch.cuda.profiler.stop()
-    barrier_sync(comm)
-    dev_ms = max_over_ranks(comm, e0.elapsed_time(e1), device)
-    clk = clocks.stop() if clocks else None
+    ms, region = timed_windows(comm, pipe.step, K, nw, pipe.engine.depth, device, profiler_range)
     h, m, b = cache.stats(reset=True)
-    gather_ms = float(np.mean(pipe.gather_ms()))
-    sample_ms = float(np.mean(pipe.engine.sample_ms()))
-    if os.environ.get("COALA_SAMPLER_TRACE") and comm.global_rank == 0:
-        sys.stderr.write("sampler trace (ms between ops): %s\n" % ["%.4f" % x for x in pipe.engine.slots[0].sampler.trace()])
-    rows = (h + m + b) / args.steps
-    value = N * args.steps / (dev_ms * 1e-3)
+    g_ms = pipe.gather_ms()
+    s_ms = pipe.engine.sample_ms()
+    steps_done = K * nw + pipe.engine.depth
+    med = float(np.median(ms))
+    hs, ms_, bs = reduce_ranks(comm, [h, m, b], device)
+    res = {"value": comm.global_size * K / (med * 1e-3), "ms_per_step": med / K, "windows": nw, "window_steps": K,
+           "window_ms_min_med_max": [float(np.min(ms)), med, float(np.max(ms))], "mean_value_all_windows": comm.global_size * K * nw / (float(np.sum(ms)) * 1e-3),
+           "hit_ratio": hs / max(1.0, hs + ms_ + bs), "rows_per_step": (h + m + b) / steps_done, "miss_rows_per_step": (m + b) / steps_done,
+           "gather_kernel_ms": float(np.mean(g_ms)) if g_ms else None, "sample_stream_ms": float(np.mean(s_ms)) if s_ms else None,
+           "region": region}
+    return pipe, res
 
-    # ---- replay: id lists of a few more batches, sampled now and gathered afterwards one by one with nothing
-    # else running on this GPU and the ranks aligned by a barrier: the gather kernel alone, in the
-    # multi-process mapping, on real id lists (each list used once, so L2 holds none of its rows)
+
+def gather_links(res, R, G, hbm_peak, host_peak, peak_src):
+    """Per-link algorithmic bytes of one gather launch against each link's peak: a row is 2R of HBM traffic
+    (line read + output write on a hit, line write + output write on a miss), R over the host link on a miss, and R over
+    NVLink into this GPU when its owner is a peer (fraction (G-1)/G of the rows under id % G routing)."""
+    rows, miss_rows, t = res["rows_per_step"], res["miss_rows_per_step"], res["gather_kernel_ms"] * 1e-3
+    remote = (G - 1) / G
+    alg = {"hbm": 2.0 * R * rows, "host_link": R * miss_rows, "nvlink_in": R * (rows - miss_rows) * remote}
+    peaks = {"hbm": hbm_peak, "host_link": host_peak, "nvlink_in": NVL_PEAK}
+    srcs = {"hbm": peak_src, "host_link": "coala_probe_read_bandwidth (UVA streaming read, this run, all ranks probing at once)",
+            "nvlink_in": "B200_PROFILING.md measured peer copy"}
+    links = {k: {"achieved": alg[k] / t / 1e9, "peak": peaks[k], "unit": "GB/s", "frac": alg[k] / t / 1e9 / peaks[k],
+                 "alg_bytes_per_launch": alg[k], "peak_source": srcs[k]} for k in alg}
+    binding = max(alg, key=lambda k: alg[k] / peaks[k])  # the link with the largest lower bound on the kernel's time
+    return links, binding
+
+
+def limiter_of(res, depth):
+    """What bounds a step: the gather stream is serial (one launch per step), samples overlap `depth`-fold."""
+    g, s, step = res["gather_kernel_ms"] or 0.0, res["sample_stream_ms"] or 0.0, res["ms_per_step"]
+    if g >= 0.85 * step:
+        return "gather kernel (%.0f %% of the step)" % (100 * g / step)
+    if s / max(1, depth) >= 0.7 * step:
+        return "sampling chain (%.3f ms per sample, %d in flight)" % (s, depth)
+    return "mixed: gather %.3f ms, sample %.3f ms / %d in flight, step %.3f ms" % (g, s, depth, step)
+
+
+def replay_gather(comm, pipe, cache, fan, device, engines):
+    """The gather kernel alone on real id lists whose rows are resident: a few more batches are sampled now and their lists
+    gathered afterwards one by one with nothing else running on this GPU and the ranks aligned by a barrier (each list
+    is used once per engine and the other lists, ~0.7 GB, pass through L2 in between)."""
+    import torch
+    from coala_gnn_b200._lib import lib, check
     from coala_gnn_b200.pybind import tensor_from_ptr
     torch.cuda.synchronize()
     lists = []
@@ -247,144 +375,390 @@ def run_ours(args):
         check(lib().coala_sampler_counts(sl.sampler._h, cnts))
         idx_ptr, _ = sl.sampler.input_nodes_dev_ptrs()
         lists.append(tensor_from_ptr(idx_ptr, (int(cnts[0]),), torch.int64, device).clone())
-    for _ in range(3):
-        pipe.step()  # the sampled rows of the lists above are resident now; drain the prefetch
+    for _ in range(pipe.engine.depth):
+        pipe.step()  # drain the prefetch: the rows of the lists above are resident now
     torch.cuda.synchronize()
     cache.stats(reset=True)
-    replay, out_buf = [], pipe.engine.slots[0].out
-    for ids in lists:
-        barrier_sync(comm)
-        r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        r0.record()
-        cache.read_feature_async(out_buf.data_ptr(), ids.data_ptr(), ids.numel(), 0, torch.cuda.current_stream().cuda_stream)
-        r1.record()
-        torch.cuda.synchronize()
-        replay.append(r0.elapsed_time(r1))
-    replay_ms = float(np.median(replay))
-    n_last = int(np.mean([x.numel() for x in lists]))
-    rh, rm, rb = cache.stats(reset=True)
-    # the same lists once more with copy engine 1 (hit rows as bulk asynchronous copies through shared memory); the 7 other
-    # lists (~0.7 GB) have passed through L2 since a list was last touched
-    replay_e1_ms, replay_e1_err = None, "not run (multi-process runs only with COALA_BENCH_REPLAY_ENGINE1=1)"
+    out_buf = pipe.engine.slots[0].out
+    res = {"rows": int(np.mean([x.numel() for x in lists]))}
     try:
-        # engine 1 over peer mappings has been measured in-process (scripts/bench_gather.py --gpus 2), not yet across
-        # processes: a device fault there could not be caught, so multi-rank runs keep to engine 0 unless asked
-        r = []
-        use_e1 = N == 1 or os.environ.get("COALA_BENCH_REPLAY_ENGINE1") == "1"
-        if use_e1:
-            cache.set_copy_engine(1)
-        for ids in (lists if use_e1 else []):
-            barrier_sync(comm)
-            r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            r0.record()
-            cache.read_feature_async(out_buf.data_ptr(), ids.data_ptr(), ids.numel(), 0, torch.cuda.current_stream().cuda_stream)
-            r1.record()
-            torch.cuda.synchronize()
-            r.append(r0.elapsed_time(r1))
-        if r:
-            replay_e1_ms = float(np.median(r))
-    except RuntimeError as e:  # symmetric on all ranks (same launch, same arguments): the barriers stay matched
-        replay_e1_err = str(e)
+        for eng in engines:
+            cache.set_copy_engine(eng)
+            r = []
+            for ids in lists:
+                barrier_sync(comm)
+                r0, r1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                r0.record()
+                cache.read_feature_async(out_buf.data_ptr(), ids.data_ptr(), ids.numel(), 0, torch.cuda.current_stream().cuda_stream)
+                r1.record()
+                torch.cuda.synchronize()
+                r.append(r0.elapsed_time(r1))
+            h, m, b = cache.stats(reset=True)
+            res["engine_%d" % eng] = {"ms": float(np.median(r)), "hit_ratio": h / max(1, h + m + b)}
     finally:
-        cache.set_copy_engine(0)
-        cache.stats(reset=True)
+        cache.set_copy_engine(int(os.environ.get("COALA_GATHER_ENGINE", "0")))
+    return res
 
-    # ---- e2e: the drop-in iterator (host seed list, host colour metadata, per-step D2H of the result ids)
-    it = iter(loader)
-    loader.scheduler.refresh_counter = args.refresh_counter
-    pin = torch.empty(B, dtype=torch.int64).pin_memory()
 
-    def loader_steps(n):
-        nonlocal it
-        last = None
-        for _ in range(n):
-            try:
-                last = next(it)
-            except StopIteration:
-                it = iter(loader)
-                last = next(it)
-            pin.copy_(last[1], non_blocking=True)  # D2H read of the step's result header (seeds)
-        return last
+def preload_cache(comm, loader, ds, device):
+    """Fill a cache through the real gather path with every id this rank's shard owns (partitioned: id % L == rank)."""
+    import torch
+    mgr = loader.COALA_GNN_Manager
+    cache, ms = mgr.COALA_GNN_Cache, mgr.max_sample_size
+    out = mgr.out_buffers(1)[0]
+    part = mgr.cache_backend in ("nvshmem", "nccl") and comm.local_size > 1
+    ids = torch.arange(comm.local_rank if part else 0, ds.num_nodes, comm.local_size if part else 1, dtype=torch.int64, device=device)
+    st = torch.cuda.current_stream().cuda_stream
+    for lo in range(0, ids.numel(), ms):
+        chunk = ids[lo:lo + ms]
+        cache.read_feature_async(out.data_ptr(), chunk.data_ptr(), chunk.numel(), 0, st)
+    torch.cuda.synchronize()
+    cache.stats(reset=True)
 
-    loader_steps(max(3, args.warmup // 2))
+
+
+class LoaderDriver(object):
+    """Draws batches from the drop-in iterator across epochs; every step copies the result header (the seeds) back to
+    pinned host memory, the D2H read a training loop does for its loss."""
+
+    def __init__(self, loader, B):
+        import torch
+        self.loader, self.it, self.last = loader, iter(loader), None
+        self.pin = torch.empty(B, dtype=torch.int64).pin_memory()
+
+    def step(self):
+        try:
+            self.last = next(self.it)
+        except StopIteration:
+            self.it = iter(self.loader)
+            self.last = next(self.it)
+        self.pin.copy_(self.last[1], non_blocking=True)
+
+
+def measure_loader(comm, drv, K, n_windows, device, warmup):
+    """e2e-style measurement on the host clock (the iterator blocks on the sampler's counts every step, so the host clock
+    sees the device): barrier+synchronize, refill, n_windows windows of K steps, final synchronize in the last window."""
+    import torch
+    loader = drv.loader
+    cache = loader.COALA_GNN_Manager.COALA_GNN_Cache
+    for _ in range(max(3, warmup)):
+        drv.step()
     barrier_sync(comm)
     cache.stats(reset=True)
+    depth = loader.engine.depth if loader.engine is not None else 0
+    for _ in range(depth):
+        drv.step()
+    t_a = time.time()
+    stamps = [time.perf_counter()]
+    for w in range(n_windows):
+        for _ in range(K):
+            drv.step()
+        stamps.append(time.perf_counter())
+    torch.cuda.synchronize()
+    t_end = time.perf_counter()
+    region = (t_a, time.time())
+    e_ms = reduce_ranks(comm, [1e3 * (stamps[i + 1] - stamps[i]) for i in range(n_windows)], device, "max")
+    e_total = reduce_ranks(comm, [t_end - stamps[0]], device, "max")[0]
+    barrier_sync(comm)
+    h, m, b = cache.stats(reset=True)
+    hs, ms_, bs = reduce_ranks(comm, [h, m, b], device)
+    med = float(np.median(e_ms))
+    N = comm.global_size
+    return {"value": N * K / (med * 1e-3), "ms_per_step": med / K, "windows": n_windows, "mean_value_all_windows": N * K * n_windows / e_total,
+            "hit_ratio": hs / max(1.0, hs + ms_ + bs), "miss_rows_per_step": (m + b) / (K * n_windows + depth),
+            "rows_per_step": (h + m + b) / (K * n_windows + depth), "region": region}
+
+
+def check_loader(drv, chk, sampler, K, oracle_batches=4):
+    """The next K batches of the iterator, checked one by one (untimed)."""
+    import torch
+    from coala_gnn_b200.sampler import batch_key
+    loader = drv.loader
+    for i in range(K):
+        drv.step()
+        input_nodes, seeds, blocks, feat = drv.last
+        torch.cuda.synchronize()
+        chk.rows(feat.data_ptr(), input_nodes.data_ptr(), input_nodes.numel())
+        if i < oracle_batches:
+            t_eng = (loader._epoch_base + loader.counter - 1) if loader.engine is not None else sampler.calls - 1
+            chk.blocks(seeds.cpu().numpy(), batch_key(sampler.seed, t_eng, sampler.rank), input_nodes.cpu().numpy(), blocks[0].edge_src.cpu().numpy())
+    chk.tot["refused_ids"] += loader.COALA_GNN_Manager.COALA_GNN_Cache.refused_ids()
+
+
+# ------------------------------------------------------------------------------------------------------------
+# main measurement
+# ------------------------------------------------------------------------------------------------------------
+def run_ours(args, state):
+    import torch
+    from coala_gnn_b200._lib import lib, check
+    comm, ds, train, fan, nd, sampler, loader, device = build_world(args)
+    state.update(comm=comm, ds=ds)
+    N, B, R, K = comm.global_size, args.batch_size, ds.cache_dim * 4, args.steps
+    clocks = ClockSampler(comm.device_index) if comm.global_rank == 0 else None
+    cache = loader.COALA_GNN_Manager.COALA_GNN_Cache
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    hbm_peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    if os.path.exists(peaks_path):
+        hbm_peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json"
+    gb = C.c_double()
+    barrier_sync(comm)
+    check(lib().coala_probe_read_bandwidth(ds.feat_data.data_ptr(), min(ds.num_nodes * R, 4 << 30), 2, C.byref(gb)))
+    host_peak = gb.value
+
+    # ---- untimed cache pre-warm through the real path (steady state is what an epoch sees)
+    from coala_gnn_b200.pipeline import DevicePipeline
+    warm = DevicePipeline(loader, seed=77, prefetch=not args.no_prefetch)
+    t0 = time.time()
+    n_pre = 0
+    budget = args.prewarm if args.prewarm >= 0 else 10 ** 9
+    while n_pre < budget:
+        for _ in range(50):
+            warm.step()
+        torch.cuda.synchronize()
+        n_pre += 50
+        if args.prewarm < 0:  # every rank must leave after the same batch (the path holds collectives)
+            if reduce_ranks(comm, [float(time.time() - t0 > args.prewarm_seconds)], device, "max")[0] > 0:
+                break
+    rate = n_pre / max(1e-3, time.time() - t0)
+    del warm
+    cache.stats(reset=True)
+
+    # ---- value: device-resident pipeline, steady state
+    chk = Checker(comm, ds, train, fan, nd, device)
+    pipe, res = measure_pipeline(args, comm, loader, device, K, args.min_seconds, rate, args.warmup, profiler_range=args.cuda_profiler_range)
+    regions = [res.pop("region")]
+    if os.environ.get("COALA_SAMPLER_TRACE") and comm.global_rank == 0:
+        sys.stderr.write("sampler trace (ms between ops): %s\n" % ["%.4f" % x for x in pipe.engine.slots[0].sampler.trace()])
+    check_pipeline(pipe, chk, K)
+    parity_value = chk.summary()
+
+    # ---- the gather kernel alone on resident rows, both copy engines
+    use_e1 = N == 1 or os.environ.get("COALA_BENCH_REPLAY_ENGINE1", "1") == "1"
+    replay = replay_gather(comm, pipe, cache, fan, device, [0, 1] if use_e1 else [0])
+    n_last = replay["rows"]
+
+    # ---- e2e: the drop-in iterator (host seed list, host colour metadata, per-step D2H of the result header)
+    loader.scheduler.refresh_counter = args.refresh_counter
+    drv = LoaderDriver(loader, B)
+    nw_e = n_windows_for(comm, res["value"] / N, K, args.min_seconds, device)
     prof = None
     if args.profile_e2e and comm.global_rank == 0:
         import cProfile
         prof = cProfile.Profile()
         prof.enable()
-    t0 = time.perf_counter()
-    loader_steps(args.steps)
-    torch.cuda.synchronize()
-    e2e_local = time.perf_counter() - t0
+    e2e = measure_loader(comm, drv, K, nw_e, device, args.warmup)
     if prof is not None:
         import pstats
         prof.disable()
         pstats.Stats(prof, stream=sys.stderr).sort_stats("cumulative").print_stats(35)
-    e2e_s = max_over_ranks(comm, e2e_local, device)
-    barrier_sync(comm)
-    eh, em, eb = cache.stats(reset=True)
-    e2e_value = N * args.steps / e2e_s
+    regions.append(e2e.pop("region"))
+    chk2 = Checker(comm, ds, train, fan, nd, device)
+    check_loader(drv, chk2, sampler, K)
+    parity_e2e = chk2.summary()
+    clk = clocks.stop(regions) if clocks else None
+
     L = comm.local_size
     # per step and rank: seeds H2D through the pinned staging buffer; D2H of the block counts, of the step header the loop
     # reads back, and (every refresh_counter steps) of the cache colour histogram
     h2d = B * 8
     d2h = B * 8 + 8 * (2 * len(fan) + 1) + nd.meta_len * 4 / args.refresh_counter
-
-    hs, ms_, bs = sum_over_ranks(comm, [h, m, b], device)
     out = None
+    G = L if args.cache_backend in ("nvshmem", "p2p") else 1
+    remote = (G - 1) / G
+    links, binding = gather_links(res, R, G, hbm_peak, host_peak, peak_src)
+    state.update(train=train, fan=fan, device=device, hbm_peak=hbm_peak, host_peak=host_peak, peak_src=peak_src, rate=res["value"] / N,
+                 main_res=res, main_loader=loader, main_pipe=pipe)
     if comm.global_rank == 0:
-        # per-link algorithmic bytes of one gather launch: a row is 2R of HBM traffic (line read +
-        # output write on a hit, line write + output write on a miss), R over the host link on a miss, and R over
-        # NVLink into this GPU when its owner is a peer (fraction (G-1)/G of the rows under id % G routing)
-        miss_rows = (m + b) / args.steps
-        G = comm.local_size if args.cache_backend in ("nvshmem", "p2p") else 1
-        remote = (G - 1) / G
-        alg = {"hbm": 2.0 * R * rows, "host_link": R * miss_rows, "nvlink_in": R * (rows - miss_rows) * remote}
-        nvl_peak = 770.0  # measured peer-copy figure of B200_PROFILING.md (900 nominal); scripts/bench_gather.py reads 777 with a kernel
-        peaks = {"hbm": hbm_peak, "host_link": host_peak, "nvlink_in": nvl_peak}
-        srcs = {"hbm": peak_src, "host_link": "coala_probe_read_bandwidth (UVA streaming read, this run)",
-                "nvlink_in": "B200_PROFILING.md measured peer copy"}
-        t_meas = gather_ms * 1e-3
-        links = {k: {"achieved": alg[k] / t_meas / 1e9, "peak": peaks[k], "unit": "GB/s", "frac": alg[k] / t_meas / 1e9 / peaks[k],
-                     "alg_bytes_per_launch": alg[k], "peak_source": srcs[k]} for k in alg}
-        binding = max(alg, key=lambda k: alg[k] / peaks[k])  # the link with the largest lower bound on the kernel's time
-        hbm_replay = 2.0 * R * n_last / (replay_ms * 1e-3) / 1e9
         # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this same workload
         # (profiles/r1b_gather_full_raw.csv: 77.1 MB + 88.9 MB); only quoted for the configuration it was captured on
         traffic = 166.0e6 if (N == 1 and args.shape == "igb-medium" and args.cache_size == 16384 and args.fan_out == "5,5" and B == 1024) else None
+        t_meas = res["gather_kernel_ms"] * 1e-3
+
+        def replay_block(r):
+            return {"ms": r["ms"], "hit_ratio": r["hit_ratio"],
+                    "hbm": {"achieved": 2.0 * R * n_last / (r["ms"] * 1e-3) / 1e9, "peak": hbm_peak, "frac": 2.0 * R * n_last / (r["ms"] * 1e-3) / 1e9 / hbm_peak},
+                    "nvlink_in": {"achieved": R * n_last * remote / (r["ms"] * 1e-3) / 1e9, "peak": NVL_PEAK, "frac": R * n_last * remote / (r["ms"] * 1e-3) / 1e9 / NVL_PEAK}}
         out = {
-            "metric": METRIC, "value": value, "unit": "mini-batches/s", "n_gpus": N, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
+            "metric": METRIC, "value": res["value"], "unit": "mini-batches/s", "n_gpus": N, "steps": K, "warmup": args.warmup,
+            "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "ours",
             "config": {"workload": "%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), SAGE fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
                        % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, B, args.cache_size, args.cache_backend, comm.num_master_process, L, args.distribution),
-                       "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (a different row set every step; the table is %.0f GB, L2 is 126 MB)" % (rows * R / 1e6, ds.num_nodes * R / 1e9),
+                       "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (a different row set every step; the table is %.0f GB, L2 is 126 MB)" % (res["rows_per_step"] * R / 1e6, ds.num_nodes * R / 1e9),
                        "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter,
+                       "colour_metadata": ds.color_source,
                        "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr copy in HBM" if sampler.hbm_indptr else "")},
-            "hit_ratio": hs / max(1.0, hs + ms_ + bs), "rows_per_step": rows,
-            "gather_GBs": rows * R / t_meas / 1e9, "sample_stream_ms": sample_ms,
+            "timing": {"protocol": "barrier+synchronize, %d untimed refill steps, then %d back-to-back windows of %d steps (one CUDA event per window on the consumer stream, "
+                                   "no drain in between), barrier+synchronize; max over ranks per window; value = median window" % (pipe.engine.depth, res["windows"], K),
+                       "windows": res["windows"], "window_ms_min_med_max": res["window_ms_min_med_max"], "mean_value_all_windows": res["mean_value_all_windows"],
+                       "scaling_refers_to": "this line: %d MB cache per GPU, so the per-GPU hit ratio rises with N (capacity effect); extras.all_resident is the same-regime line" % args.cache_size},
+            "hit_ratio": res["hit_ratio"], "rows_per_step": res["rows_per_step"],
+            "gather_GBs": res["rows_per_step"] * R / t_meas / 1e9, "sample_stream_ms": res["sample_stream_ms"],
+            "limiter": limiter_of(res, pipe.engine.depth),
+            "parity": {"value_leg": parity_value, "e2e_leg": parity_e2e,
+                       "rows_checked": parity_value["rows_checked"] + parity_e2e["rows_checked"],
+                       "mismatches": parity_value["mismatches"] + parity_e2e["mismatches"] + parity_value["block_mismatches"] + parity_e2e["block_mismatches"]
+                       + parity_value["seed_mismatches"] + parity_e2e["seed_mismatches"],
+                       "ranks": N, "sampler_note": "blocks are compared with this repo's CPU restatement of DGL's documented semantics (DGL is absent: parity with DGL itself is unpinned)"},
             # the dominant kernel against the link that bounds it (SURVEY.md 8d: T_bound = max over links of bytes/peak);
             # `hbm` is always listed too, and `all_hit_replay` times the same kernel on resident rows (the HBM / NVLink regime)
             "roofline": {"bound": binding, "achieved": links[binding]["achieved"], "peak": links[binding]["peak"], "unit": "GB/s",
                          "frac": links[binding]["frac"], "traffic": traffic, "peak_source": links[binding]["peak_source"],
-                         "kernel": "coala_gather_kernel", "kernel_ms": gather_ms, "kernel_share_of_step": gather_ms / (dev_ms / args.steps),
+                         "kernel": "coala_gather_kernel", "kernel_ms": res["gather_kernel_ms"], "kernel_share_of_step": res["gather_kernel_ms"] / res["ms_per_step"],
                          "links": links,
-                         "all_hit_replay": {"ms": replay_ms, "rows": n_last, "hit_ratio": rh / max(1, rh + rm + rb),
-                                            "copy_engine_1": ({"ms": replay_e1_ms, "hbm_frac": 2.0 * R * n_last / (replay_e1_ms * 1e-3) / 1e9 / hbm_peak,
-                                                               "nvlink_in_frac": R * n_last * remote / (replay_e1_ms * 1e-3) / 1e9 / nvl_peak}
-                                                              if replay_e1_ms else {"error": replay_e1_err}),
-                                            "hbm": {"achieved": hbm_replay, "peak": hbm_peak, "frac": hbm_replay / hbm_peak},
-                                            "nvlink_in": {"achieved": R * n_last * remote / (replay_ms * 1e-3) / 1e9, "peak": nvl_peak,
-                                                          "frac": R * n_last * remote / (replay_ms * 1e-3) / 1e9 / nvl_peak}}},
-            "e2e": {"value": e2e_value, "unit": "mini-batches/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-                    "host_link_feature_bytes_per_step": int(R * (em + eb) / args.steps), "hit_ratio": eh / max(1, eh + em + eb),
+                         "all_hit_replay": dict(rows=n_last, **{k: replay_block(v) for k, v in replay.items() if k.startswith("engine_")})},
+            "e2e": {"value": e2e["value"], "unit": "mini-batches/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+                    "windows": nw_e, "mean_value_all_windows": e2e["mean_value_all_windows"],
+                    "host_link_feature_bytes_per_step": int(R * e2e["miss_rows_per_step"]), "hit_ratio": e2e["hit_ratio"],
                     "api": "COALA_GNN_DataLoader.__next__"},
-            "gpu_launches": pipe.kernels_per_step * args.steps,
+            "gpu_launches": pipe.kernels_per_step * K * res["windows"],
+            "gpu_launches_per_step": pipe.kernels_per_step,
             "clocks": clk,
         }
-    return comm, ds, train, fan, out
+    return out
+
+
+# ------------------------------------------------------------------------------------------------------------
+# extras: the other regimes of the reference's experiment matrix, measured the same way in the same process
+# ------------------------------------------------------------------------------------------------------------
+def summarize(res, pipe, R, G, st):
+    links, binding = gather_links(res, R, G, st["hbm_peak"], st["host_peak"], st["peak_src"])
+    return {"value": res["value"], "ms_per_step": res["ms_per_step"], "hit_ratio": res["hit_ratio"], "windows": res["windows"],
+            "gather_kernel_ms": res["gather_kernel_ms"], "sample_stream_ms": res["sample_stream_ms"], "rows_per_step": res["rows_per_step"],
+            "binding_link": binding, "binding_link_frac": links[binding]["frac"], "binding_link_GBs": links[binding]["achieved"],
+            "limiter": limiter_of(res, pipe.engine.depth)}
+
+
+def extra_all_resident(args, st):
+    """Same-regime scaling line: the cache of every N holds the whole table (hit ratio 1.0), so 1 -> 8 compares like with like."""
+    import torch
+    comm, ds, device = st["comm"], st["ds"], st["device"]
+    R, K, L = ds.cache_dim * 4, args.steps, comm.local_size
+    if st["main_res"]["hit_ratio"] >= 0.9995:
+        return dict(summarize(st["main_res"], st["main_pipe"], R, L, st), cache_mb_per_gpu=args.cache_size, same_run_as_main_line=True)
+    lines_needed = ds.num_nodes / L
+    mb = int(math.ceil(lines_needed * 1.2 * R / (1 << 20) / 1024.0)) * 1024
+    _, _, _, fan, nd, sampler, loader, _ = build_world(args, comm=comm, ds=ds, cache_size=mb)
+    preload_cache(comm, loader, ds, device)
+    pipe, res = measure_pipeline(args, comm, loader, device, K, 1.0, 4000.0, args.warmup, seed=2002)
+    res.pop("region")
+    chk = Checker(comm, ds, st["train"], fan, nd, device)
+    check_pipeline(pipe, chk, min(K, 8), oracle_batches=2)
+    replay = replay_gather(comm, pipe, loader.COALA_GNN_Manager.COALA_GNN_Cache, fan, device, [0, 1])
+    out = dict(summarize(res, pipe, R, L, st), cache_mb_per_gpu=mb, same_run_as_main_line=False, parity=chk.summary())
+    n_last = replay["rows"]
+    for k, v in replay.items():
+        if k.startswith("engine_"):
+            out["gather_alone_" + k] = {"ms": v["ms"], "hbm_frac": 2.0 * R * n_last / (v["ms"] * 1e-3) / 1e9 / st["hbm_peak"],
+                                       "nvlink_in_frac": R * n_last * (L - 1) / L / (v["ms"] * 1e-3) / 1e9 / NVL_PEAK, "rows": n_last}
+    del pipe, loader
+    torch.cuda.empty_cache()
+    return out
+
+
+def extra_distribution(args, st):
+    """The reference's headline comparison (examples/Distribution_compare_script.sh:26-35): node_color vs baseline over D x L
+    cache domains at 4096 MB per GPU, colour metadata from the colouring of the graph.  Stage 1 does real work here:
+    nd_score_kernel / nd_assign_kernel run every step on the domain histograms refreshed every `refresh_counter` batches."""
+    import torch
+    from COALA_GNN import MPI_Comm_Manager
+    comm0, ds, device = st["comm"], st["ds"], st["device"]
+    N, K, R = comm0.global_size, args.steps, ds.cache_dim * 4
+    layouts = [L for L in (1, 2, 4) if N % L == 0 and N // L >= 2]
+    out = {"cache_mb_per_gpu": 4096, "colour_metadata": ds.color_source, "layouts": {}}
+    for L in layouts:
+        comm = MPI_Comm_Manager(-1, gpus_per_domain=L)
+        row = {}
+        for method in ("baseline", "node_color"):
+            _, _, _, fan, nd, sampler, loader, _ = build_world(args, comm=comm, ds=ds, cache_size=4096, backend="nvshmem", distribution=method)
+            from coala_gnn_b200.pipeline import DevicePipeline
+            warm = DevicePipeline(loader, seed=55)
+            for _ in range(1200):  # several cache turnovers: 1 M lines per GPU, ~2e4 fills per batch
+                warm.step()
+            torch.cuda.synchronize()
+            del warm
+            pipe, res = measure_pipeline(args, comm, loader, device, K, 1.0, 1000.0, args.warmup, seed=3003)
+            res.pop("region")
+            chk = Checker(comm, ds, st["train"], fan, nd, device)
+            check_pipeline(pipe, chk, min(K, 8), oracle_batches=3)
+            row[method] = dict(summarize(res, pipe, R, L, st), parity=chk.summary(), gpu_launches_per_step=pipe.kernels_per_step)
+            if method == "node_color":  # stage 1 alone: score + assign of one global batch, on this rank
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                dom = pipe.domain_seeds[0]
+                ptrs = [pipe.meta[d].data_ptr() for d in range(pipe.D)]
+                torch.cuda.synchronize()
+                e0.record()
+                for _ in range(20):
+                    nd.distribute_manager.distribute_async(0, dom.data_ptr(), ptrs, torch.cuda.current_stream().cuda_stream, slot=1)
+                e1.record()
+                torch.cuda.synchronize()
+                row[method]["distribute_kernels_ms"] = e0.elapsed_time(e1) / 20
+            del pipe, loader, nd
+            torch.cuda.empty_cache()
+        row["hit_ratio_gain"] = row["node_color"]["hit_ratio"] - row["baseline"]["hit_ratio"]
+        row["speedup_node_color_over_baseline"] = row["node_color"]["value"] / row["baseline"]["value"]
+        out["layouts"]["%dx%d" % (N // L, L)] = row
+    return out
+
+
+def extra_backends(args, st):
+    """examples/Cache_compare_script.sh:28-35: partitioned P2P cache vs isolated caches vs the NCCL all-to-all variant, 4096 MB per GPU,
+    one domain spanning the box."""
+    import torch
+    comm, ds, device = st["comm"], st["ds"], st["device"]
+    K, R, L = args.steps, ds.cache_dim * 4, comm.local_size
+    out = {"cache_mb_per_gpu": 4096}
+    for backend in ("nvshmem", "isolated", "nccl"):
+        _, _, _, fan, nd, sampler, loader, _ = build_world(args, comm=comm, ds=ds, cache_size=4096, backend=backend)
+        chk = Checker(comm, ds, st["train"], fan, nd, device)
+        if loader.engine is None:  # a backend outside the prefetch engine: through the iterator, host clock
+            drv = LoaderDriver(loader, args.batch_size)
+            for _ in range(600):
+                drv.step()
+            res = measure_loader(comm, drv, K, n_windows_for(comm, 300.0, K, 1.0, device), device, args.warmup)
+            res.pop("region")
+            check_loader(drv, chk, sampler, min(K, 8), oracle_batches=2)
+            out[backend] = {"value": res["value"], "ms_per_step": res["ms_per_step"], "hit_ratio": res["hit_ratio"], "windows": res["windows"],
+                            "through": "COALA_GNN_DataLoader iterator (host clock)", "parity": chk.summary()}
+            del drv, loader, nd
+            torch.cuda.empty_cache()
+            continue
+        from coala_gnn_b200.pipeline import DevicePipeline
+        warm = DevicePipeline(loader, seed=66)
+        for _ in range(1200):
+            warm.step()
+        torch.cuda.synchronize()
+        del warm
+        pipe, res = measure_pipeline(args, comm, loader, device, K, 1.0, 1000.0, args.warmup, seed=4004)
+        res.pop("region")
+        check_pipeline(pipe, chk, min(K, 8), oracle_batches=2)
+        out["p2p" if backend == "nvshmem" else backend] = dict(summarize(res, pipe, R, L if backend == "nvshmem" else 1, st), parity=chk.summary(),
+                                                               through="DevicePipeline (CUDA events)")
+        del pipe, loader, nd
+        torch.cuda.empty_cache()
+    return out
+
+
+def run_extras(args, st, out):
+    comm = st["comm"]
+    N = comm.global_size
+    want = args.extras
+    if want == "none":
+        return
+    names = ["all_resident"] + (["distribution", "backends"] if N >= 2 else [])
+    if want != "auto":
+        names = [n for n in want.split(",") if n in ("all_resident", "distribution", "backends") and (N >= 2 or n == "all_resident")]
+    if comm.num_master_process != 1:
+        names = [n for n in names if n == "all_resident"]
+    extras = {}
+    fns = {"all_resident": extra_all_resident, "distribution": extra_distribution, "backends": extra_backends}
+    for n in names:
+        t0 = time.time()
+        extras[n] = fns[n](args, st)
+        if isinstance(extras[n], dict):
+            extras[n]["seconds"] = round(time.time() - t0, 1)
+        if out is not None:
+            out["extras"] = extras  # visible to the watchdog as soon as a section is complete
 
 
 def main():
@@ -402,6 +776,7 @@ def main():
         from coala_gnn_b200.datasets import SyntheticSharedCSCUVA
         from coala_gnn_b200 import synth
         comm = MPI_Comm_Manager(0)
+        os.environ["COALA_SYNTH_COLOR"] = "block"  # the CPU arm never reads colour metadata
         ds = SyntheticSharedCSCUVA(args.shape, comm, "cuda:0", verbose=True)
         try:
             fan = [int(f) for f in args.fan_out.split(",")]
@@ -410,7 +785,7 @@ def main():
             line = {"metric": METRIC, "value": r["batches_per_s"], "unit": "mini-batches/s", "n_gpus": args.gpus, "steps": args.steps,
                     "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                     "dtype": "f32", "data": "synthetic", "impl": "reference",
-                    "config": {"workload": "%s, SAGE fan-out %s, batch %d: CPU sampler (OpenMP restatement of the DGL CPU sampler, DGL absent) + index_select gather on %d host threads"
+                    "config": {"workload": "%s, SAGE fan-out %s, batch %d: CPU sampler (OpenMP restatement of the DGL CPU sampler, DGL absent) + torch.index_select gather on %d host threads"
                                % (args.shape, args.fan_out, args.batch_size, r["threads"])},
                     "cpu_baseline": {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
                                      "sample": "%d mini-batches of %d seeds (%.0f gathered rows each)" % (r["steps"], args.batch_size, r["rows_per_step"])},
@@ -425,26 +800,65 @@ def main():
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus), "--master-addr", "127.0.0.1",
                "--master-port", "29511", os.path.abspath(__file__)] + sys.argv[1:]
         return subprocess.call(cmd)
-    comm = ds = None
+    state = {}
+    printed = threading.Event()
+    out_box = [None]
+
+    def emit(note=None):
+        if printed.is_set():
+            return
+        printed.set()
+        if out_box[0] is not None:
+            if note:
+                out_box[0].setdefault("extras", {})["abandoned"] = note
+            print(json.dumps(out_box[0]), flush=True)
+
+    def bail():  # the extras must never cost the main line: print what is complete and leave (every rank has the same timer)
+        emit("extras exceeded --extras_budget of %.0f s; sections listed are complete" % args.extras_budget)
+        ds = state.get("ds")
+        try:
+            if ds is not None:
+                ds.unlink_segments()  # kernels may still be reading the mappings: drop the names only
+        finally:
+            os._exit(0)
+
+    comm = None
     try:
-        comm, ds, train, fan, out = run_ours(args)
+        out_box[0] = run_ours(args, state)
+        comm = state["comm"]
+        timer = threading.Timer(args.extras_budget, bail)
+        timer.daemon = True
+        timer.start()
+        try:
+            run_extras(args, state, out_box[0])
+        finally:
+            timer.cancel()
         if comm.global_rank == 0:
+            ds, train, fan = state["ds"], state["train"], state["fan"]
             if world == 1 and not args.no_cpu_baseline:
                 r = cpu_path((ds.csc_host[0], ds.csc_host[1], ds.feat_host_array()), train.numpy(), args.batch_size, fan,
                              seconds=args.cpu_baseline_seconds)
-                out["cpu_baseline"] = {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
-                                       "sample": "%d mini-batches of %d seeds in %.1f s (oracle OpenMP sampler + index_select, %.1f GB/s gathered)"
-                                                 % (r["steps"], args.batch_size, r["steps"] / r["batches_per_s"], r["gather_GBs"])}
-            print(json.dumps(out), flush=True)
+                out_box[0]["cpu_baseline"] = {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
+                                              "sample": "%d mini-batches of %d seeds in %.1f s (oracle OpenMP sampler + torch.index_select, %.1f GB/s gathered)"
+                                                        % (r["steps"], args.batch_size, r["steps"] / r["batches_per_s"], r["gather_GBs"])}
+            emit()
     finally:
+        comm = state.get("comm")
         if comm is not None and comm.global_size > 1:
             import torch.distributed as dist
             try:
                 dist.barrier()
             except Exception:
                 pass
+        ds = state.get("ds")
         if ds is not None:
             ds.cleanup()
+        if comm is not None and comm.global_size > 1:
+            try:
+                import torch.distributed as dist
+                dist.destroy_process_group()
+            except Exception:
+                pass
     return 0
 
 

@@ -26,6 +26,7 @@ SIGNATURES = {
     "coala_nd_create_plain": (_vp, [_u64, _i32]),
     "coala_nd_distribute": (_i32, [_vp, _u64, _u64, _vp, _i32]),
     "coala_nd_distribute_async": (_i32, [_vp, _u64, _u64, _vp, _i32, _vp]),
+    "coala_nd_distribute_async_slot": (_i32, [_vp, _u64, _u64, _vp, _i32, _i32, _vp]),
     "coala_nd_set_meta_len": (_i32, [_vp, _i32]),
     "coala_nd_last_bucket_len": (_i32, [_vp, _vp]),
     "coala_nd_num_colors": (_i32, [_vp]),
@@ -45,6 +46,8 @@ SIGNATURES = {
     "coala_cache_attach_fd": (_i32, [_vp, _i32, _i32]),
     "coala_cache_read_feature": (_i32, [_vp, _u64, _u64, _i64]),
     "coala_cache_read_feature_async": (_i32, [_vp, _u64, _u64, _i64, _u64, _vp]),
+    "coala_cache_set_num_nodes": (_i32, [_vp, _i64]),
+    "coala_cache_refused_ids": (_i32, [_vp, _vp, _i32]),
     "coala_cache_read_feature_serial": (_i32, [_vp, _u64, _u64, _i64]),
     "coala_cache_get_cache_data": (_i32, [_vp, _u64]),
     "coala_cache_get_cache_data_n": (_i32, [_vp, _u64, _i32]),

@@ -236,6 +236,11 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     p.out_dim = feat_dim < cache_dim ? feat_dim : cache_dim;
     p.stats = c->d_stats;
     p.zero = 0;
+    // ids are bounds-checked on the device: against the tag's id field always, against the table's row count as
+    // soon as it is known (from the distributor's colour table, or coala_cache_set_num_nodes)
+    p.id_limit = TAG_ID_MASK;
+    if (nd && coala_nd_num_graph_nodes(nd) > 0 && (uint64_t)coala_nd_num_graph_nodes(nd) < p.id_limit)
+        p.id_limit = (uint64_t)coala_nd_num_graph_nodes(nd);
     if (const char* e = getenv("COALA_GATHER_MINB")) c->min_blocks = atoi(e) == 2 ? 2 : 3;
     if (const char* e = getenv("COALA_GATHER_CTAS_PER_SM")) c->ctas_per_sm = atoi(e);
     if (const char* e = getenv("COALA_GATHER_ENGINE")) c->copy_engine = atoi(e) == 1 ? 1 : 0;
@@ -360,10 +365,34 @@ extern "C" int coala_cache_read_feature_async(coala_cache* c, uint64_t out_ptr, 
                            reinterpret_cast<const int64_t*>(n_dev_ptr), static_cast<cudaStream_t>(stream), false);
 }
 
+static int fail_on_refused_ids(coala_cache* c, const char* what) {
+    unsigned long long bad = 0;
+    COALA_CUDA(cudaMemcpy(&bad, c->d_stats + 3, sizeof(bad), cudaMemcpyDeviceToHost));
+    if (bad == 0) return 0;
+    COALA_CUDA(cudaMemset(c->d_stats + 3, 0, sizeof(bad)));
+    COALA_FAIL(std::string(what) + ": " + std::to_string(bad) + " node id(s) outside [0, " + std::to_string(c->params.id_limit) +
+               ") were refused (their output rows are zero)");
+}
+
+extern "C" int coala_cache_set_num_nodes(coala_cache* c, int64_t num_nodes) {
+    if (num_nodes <= 0) COALA_FAIL("set_num_nodes: the host table has at least one row");
+    c->params.id_limit = (uint64_t)num_nodes < TAG_ID_MASK ? (uint64_t)num_nodes : TAG_ID_MASK;
+    return 0;
+}
+
+extern "C" int coala_cache_refused_ids(coala_cache* c, uint64_t* count, int reset) {
+    COALA_CUDA(cudaSetDevice(c->device));
+    unsigned long long bad = 0;
+    COALA_CUDA(cudaMemcpy(&bad, c->d_stats + 3, sizeof(bad), cudaMemcpyDeviceToHost));
+    if (count) *count = bad;
+    if (reset && bad) COALA_CUDA(cudaMemset(c->d_stats + 3, 0, sizeof(bad)));
+    return 0;
+}
+
 extern "C" int coala_cache_read_feature(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n) {
     if (coala_cache_read_feature_async(c, out_ptr, idx_ptr, n, 0, nullptr)) return -1;
     COALA_CUDA(cudaDeviceSynchronize());  // synchronous like the reference (M/ssd_gnn_cache.cuh:266)
-    return 0;
+    return fail_on_refused_ids(c, "read_feature");
 }
 
 extern "C" int coala_cache_read_feature_serial(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n) {
@@ -372,7 +401,7 @@ extern "C" int coala_cache_read_feature_serial(coala_cache* c, uint64_t out_ptr,
     if (dispatch_gather(c, reinterpret_cast<const int64_t*>(idx_ptr), reinterpret_cast<float*>(out_ptr), n, nullptr, nullptr, true))
         return -1;
     COALA_CUDA(cudaDeviceSynchronize());
-    return 0;
+    return fail_on_refused_ids(c, "read_feature_serial");
 }
 
 extern "C" int coala_cache_get_cache_data(coala_cache* c, uint64_t dst_ptr) {
@@ -410,7 +439,7 @@ extern "C" int coala_cache_stats(coala_cache* c, uint64_t* hit, uint64_t* miss, 
     if (hit) *hit = h[0];
     if (miss) *miss = h[1];
     if (bypass) *bypass = h[2];
-    if (reset) COALA_CUDA(cudaMemset(c->d_stats, 0, sizeof(h)));
+    if (reset) COALA_CUDA(cudaMemset(c->d_stats, 0, 3 * sizeof(unsigned long long)));  // [3] (refused ids) is read by its own call
     return 0;
 }
 

@@ -48,7 +48,8 @@ struct CacheParams {
     int track_color;
     int out_stride;          // floats between output rows (= feat_dim)
     int out_dim;             // floats copied per output row (min(feat_dim, cache_dim))
-    unsigned long long* stats;  // [0]=hit [1]=miss [2]=bypass
+    unsigned long long* stats;  // [0]=hit [1]=miss [2]=bypass [3]=ids refused (>= id_limit)
+    uint64_t id_limit;       // ids >= id_limit are refused: min(rows of the host table, 2^40 - 1 = the tag's id field)
     uint32_t zero;           // always 0 at run time; unknown to the compiler (see read_line_validated)
 };
 
@@ -228,6 +229,12 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
     return 1;
 }
 
+// An id outside the host table (or wider than the tag's 40-bit id field) must not be dereferenced: its output
+// row is zero-filled and the launch counts it in stats[3]; the synchronous entry points turn that into an error.
+__device__ __forceinline__ void refuse_row(const CacheParams& p, float* out_row, unsigned lane) {
+    for (int e = (int)lane; e < p.out_dim; e += 32) out_row[e] = 0.0f;
+}
+
 // Work split: the rows are cut into one contiguous chunk per warp from the DEVICE-side row count,
 // so the same launch shape serves any n (the count comes from the sampler and never visits the
 // host).  Within a chunk lane l owns row l's id and does the 64-bit owner/set arithmetic for it
@@ -247,7 +254,7 @@ __global__ void __launch_bounds__(256, MINB) coala_gather_kernel(CacheParams p, 
     const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
     const int64_t rpw = (n + warps_total - 1) / warps_total;
     const int64_t end = min(n, (w + 1) * rpw);
-    unsigned n_hit = 0, n_miss = 0, n_byp = 0;
+    unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
     for (int64_t base = w * rpw; base < end; base += 32) {
         const int cnt = (int)min((int64_t)32, end - base);
         uint64_t my_id = 0;
@@ -272,10 +279,16 @@ __global__ void __launch_bounds__(256, MINB) coala_gather_kernel(CacheParams p, 
                 set_n = __shfl_sync(0xffffffffu, my_set, i + 1);
                 t_n = ld_relaxed_u64<SYS>(p.shard[g_n].tags + (uint64_t)set_n * COALA_WAYS + lane);
             }
-            const int res = resolve_row<VPL, SYS>(p, id, g, set, t, out + (base + i) * (int64_t)p.out_stride, lane);
-            n_hit += res == 0;
-            n_miss += res == 1;
-            n_byp += res == 2;
+            float* out_row = out + (base + i) * (int64_t)p.out_stride;
+            if (id < p.id_limit) {
+                const int res = resolve_row<VPL, SYS>(p, id, g, set, t, out_row, lane);
+                n_hit += res == 0;
+                n_miss += res == 1;
+                n_byp += res == 2;
+            } else {
+                refuse_row(p, out_row, lane);
+                n_bad++;
+            }
             id = id_n; g = g_n; set = set_n; t = t_n;
         }
     }
@@ -283,6 +296,7 @@ __global__ void __launch_bounds__(256, MINB) coala_gather_kernel(CacheParams p, 
         if (n_hit) atomicAdd(&s_stat[0], n_hit);
         if (n_miss) atomicAdd(&s_stat[1], n_miss);
         if (n_byp) atomicAdd(&s_stat[2], n_byp);
+        if (n_bad) atomicAdd(p.stats + 3, (unsigned long long)n_bad);
     }
     __syncthreads();
     if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
@@ -356,7 +370,7 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
     const int64_t rpw = (n + warps_total - 1) / warps_total;
     const int64_t end = min(n, (w + 1) * rpw);
     const uint32_t out_bytes = (uint32_t)p.out_dim * 4;
-    unsigned n_hit = 0, n_miss = 0, n_byp = 0;
+    unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
     unsigned phase_bits = 0;   // bit b = parity the next wait on buffer b expects
     unsigned cur = 0;          // buffer of the next load
     BulkPending q0, q1;        // q0 = oldest waiting row, q1 = the one behind it (NBUF == 3)
@@ -372,7 +386,7 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
         const ShardView& sh = p.shard[g];
         float* out_row = out + (int64_t)q0.row * (int64_t)p.out_stride;
         const uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + (uint64_t)q0.set * COALA_WAYS + way);
-        if (t2 == q0.tw) {
+        if (__all_sync(0xffffffffu, t2 == q0.tw)) {  // one decision per warp: the else-branch runs warp-wide collectives
             if (lane == 0) bulk_store(out_row, mybuf + (size_t)buf * p.row_bytes, out_bytes);
             count(0);
         } else {  // the line changed under the copy: redo the row through the register path
@@ -410,7 +424,10 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
             const unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
             const unsigned way = m ? __ffs(m) - 1 : 0;
             const uint64_t tw = __shfl_sync(0xffffffffu, t, way);
-            if (m && ((tw >> TAG_VER_SHIFT) & 1) == 0) {
+            if (id >= p.id_limit) {
+                refuse_row(p, out + (base + i) * (int64_t)p.out_stride, lane);
+                n_bad++;
+            } else if (m && ((tw >> TAG_VER_SHIFT) & 1) == 0) {
                 // buffer `cur` belonged to a row completed at least one iteration ago
                 if (lane == 0) {
                     bulk_wait_read_all();  // ... and the store that drained it has read it
@@ -437,6 +454,7 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
         if (n_hit) atomicAdd(&s_stat[0], n_hit);
         if (n_miss) atomicAdd(&s_stat[1], n_miss);
         if (n_byp) atomicAdd(&s_stat[2], n_byp);
+        if (n_bad) atomicAdd(p.stats + 3, (unsigned long long)n_bad);
     }
     __syncthreads();
     if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);

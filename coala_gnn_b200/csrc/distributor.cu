@@ -20,6 +20,7 @@ namespace {
 
 constexpr int ND_MAX_DOMAINS = 16;
 constexpr int ND_TILE = 1024;
+constexpr int ND_SLOTS = 8;
 
 struct MetaPtrs {
     const int32_t* p[ND_MAX_DOMAINS];
@@ -166,15 +167,25 @@ struct coala_nd {
     int32_t* d_topk = nullptr;
     double* d_score = nullptr;
     int64_t* d_items = nullptr;   // staging for host-resident seed lists
-    double* d_scores = nullptr;
+    // scratch of one distribution: slot 0 belongs to the synchronous entry point, the others are handed out
+    // to callers that keep several distributions in flight on different streams (one per prefetch slot)
+    double* d_scores[ND_SLOTS] = {nullptr};
+    int* d_flags[ND_SLOTS] = {nullptr};   // [0] negative-score flag, [1..D] bucket_len
     int32_t* d_meta = nullptr;    // staging [D][meta_len]
     int64_t* d_out = nullptr;
-    int* d_flags = nullptr;       // [0] negative-score flag, [1..D] bucket_len
     int h_bucket_len[ND_MAX_DOMAINS] = {0};
     cudaStream_t stream = nullptr;
 };
 
 const int32_t* coala_nd_color_dev_i32(coala_nd* h) { return h ? h->d_color : nullptr; }
+
+static int nd_slot_scratch(coala_nd* h, int slot) {
+    if (slot < 0 || slot >= ND_SLOTS) COALA_FAIL("distribute: scratch slot must be in [0,8)");
+    if (h->d_scores[slot]) return 0;
+    COALA_CUDA(cudaMalloc(&h->d_scores[slot], (size_t)h->N * h->n_domains * 8));
+    COALA_CUDA(cudaMalloc(&h->d_flags[slot], (1 + ND_MAX_DOMAINS) * sizeof(int)));
+    return 0;
+}
 
 static int nd_init_tables(coala_nd* h, const int64_t* color, int64_t n_nodes, const int64_t* topk, const double* score,
                           int num_colors, int K) {
@@ -204,13 +215,11 @@ static int nd_init_tables(coala_nd* h, const int64_t* color, int64_t n_nodes, co
     COALA_CUDA(cudaMalloc(&h->d_score, std::max<size_t>(8, (size_t)num_colors * K * 8)));
     COALA_CUDA(cudaMemcpy(h->d_score, score, (size_t)num_colors * K * 8, cudaMemcpyHostToDevice));
     COALA_CUDA(cudaMalloc(&h->d_items, (size_t)h->N * 8));
-    COALA_CUDA(cudaMalloc(&h->d_scores, (size_t)h->N * h->n_domains * 8));
     COALA_CUDA(cudaMalloc(&h->d_meta, (size_t)h->n_domains * (num_colors + 1) * 4));
     COALA_CUDA(cudaMemset(h->d_meta, 0, (size_t)h->n_domains * (num_colors + 1) * 4));
     COALA_CUDA(cudaMalloc(&h->d_out, (size_t)h->cap * 8));
-    COALA_CUDA(cudaMalloc(&h->d_flags, (1 + ND_MAX_DOMAINS) * sizeof(int)));
     COALA_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
-    return 0;
+    return nd_slot_scratch(h, 0);
 }
 
 static coala_nd* nd_new(uint64_t item_ptr, int node_id, int batch, int local_size, int n_domains, int device) {
@@ -262,7 +271,8 @@ extern "C" void coala_nd_destroy(coala_nd* h) {
     if (h->stream) { cudaStreamSynchronize(h->stream); cudaStreamDestroy(h->stream); }
     if (h->h_color) cudaFreeHost(h->h_color);
     cudaFree(h->d_color); cudaFree(h->d_topk); cudaFree(h->d_score); cudaFree(h->d_items);
-    cudaFree(h->d_scores); cudaFree(h->d_meta); cudaFree(h->d_out); cudaFree(h->d_flags);
+    for (int k = 0; k < ND_SLOTS; k++) { cudaFree(h->d_scores[k]); cudaFree(h->d_flags[k]); }
+    cudaFree(h->d_meta); cudaFree(h->d_out);
     delete h;
 }
 
@@ -279,26 +289,34 @@ extern "C" int coala_nd_last_bucket_len(coala_nd* h, int* out) {
     return 0;
 }
 
-static int nd_launch(coala_nd* h, const int64_t* d_items, const MetaPtrs& meta, int64_t* d_out, cudaStream_t st) {
+static int nd_launch(coala_nd* h, const int64_t* d_items, const MetaPtrs& meta, int64_t* d_out, int slot, cudaStream_t st) {
+    if (nd_slot_scratch(h, slot)) return -1;
+    double* d_scores = h->d_scores[slot];
+    int* d_flags = h->d_flags[slot];
     if (h->n_domains == 1) {
-        nd_single_domain_kernel<<<(h->cap + 255) / 256, 256, 0, st>>>(d_items, h->cap, d_out, h->d_flags + 1);
+        nd_single_domain_kernel<<<(h->cap + 255) / 256, 256, 0, st>>>(d_items, h->cap, d_out, d_flags + 1);
         COALA_CUDA(cudaGetLastError());
         return 0;
     }
     const int64_t total = h->N * h->n_domains;
-    COALA_CUDA(cudaMemsetAsync(h->d_flags, 0, (1 + ND_MAX_DOMAINS) * sizeof(int), st));
+    COALA_CUDA(cudaMemsetAsync(d_flags, 0, (1 + ND_MAX_DOMAINS) * sizeof(int), st));
     nd_score_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(d_items, h->N, h->n_domains, h->K, h->d_color, h->d_topk,
-                                                                   h->d_score, meta, h->meta_len, h->d_scores, h->d_flags);
+                                                                   h->d_score, meta, h->meta_len, d_scores, d_flags);
     COALA_CUDA(cudaGetLastError());
     // both assignment kernels are enqueued; each checks the flag so that no host round trip is needed
-    nd_assign_kernel<<<1, ND_TILE, 0, st>>>(d_items, h->N, h->n_domains, h->cap, h->node_id, h->d_scores, d_out, h->d_flags + 1, h->d_flags);
-    nd_assign_serial_kernel<<<1, 32, 0, st>>>(d_items, h->N, h->n_domains, h->cap, h->node_id, h->d_scores, d_out, h->d_flags + 1, h->d_flags);
+    nd_assign_kernel<<<1, ND_TILE, 0, st>>>(d_items, h->N, h->n_domains, h->cap, h->node_id, d_scores, d_out, d_flags + 1, d_flags);
+    nd_assign_serial_kernel<<<1, 32, 0, st>>>(d_items, h->N, h->n_domains, h->cap, h->node_id, d_scores, d_out, d_flags + 1, d_flags);
     COALA_CUDA(cudaGetLastError());
     return 0;
 }
 
 extern "C" int coala_nd_distribute_async(coala_nd* h, uint64_t offset, uint64_t out_dev_ptr, const uint64_t* meta_dev_ptrs,
                                          int n_meta, void* stream) {
+    return coala_nd_distribute_async_slot(h, offset, out_dev_ptr, meta_dev_ptrs, n_meta, 1, stream);
+}
+
+extern "C" int coala_nd_distribute_async_slot(coala_nd* h, uint64_t offset, uint64_t out_dev_ptr, const uint64_t* meta_dev_ptrs,
+                                              int n_meta, int slot, void* stream) {
     // all pointers are device addresses; the seed list itself must be device-resident too
     if (!h->has_color) COALA_FAIL("Error: Node_distributor_pybind is not created with color information.");
     if (n_meta != h->n_domains) COALA_FAIL("distribute: need one cache-meta pointer per domain");
@@ -306,7 +324,7 @@ extern "C" int coala_nd_distribute_async(coala_nd* h, uint64_t offset, uint64_t 
     MetaPtrs meta;
     for (int j = 0; j < ND_MAX_DOMAINS; j++) meta.p[j] = j < n_meta ? reinterpret_cast<const int32_t*>(meta_dev_ptrs[j]) : nullptr;
     return nd_launch(h, reinterpret_cast<const int64_t*>(h->item_ptr) + offset, meta, reinterpret_cast<int64_t*>(out_dev_ptr),
-                     static_cast<cudaStream_t>(stream));
+                     slot, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" int coala_nd_distribute(coala_nd* h, uint64_t offset, uint64_t out_ptr, const uint64_t* meta_ptrs, int n_meta) {
@@ -335,9 +353,9 @@ extern "C" int coala_nd_distribute(coala_nd* h, uint64_t offset, uint64_t out_pt
     void* out = reinterpret_cast<void*>(out_ptr);
     const bool out_dev = coala_is_device_ptr(out);
     int64_t* d_out = out_dev ? static_cast<int64_t*>(out) : h->d_out;
-    if (nd_launch(h, d_items, meta, d_out, st)) return -1;
+    if (nd_launch(h, d_items, meta, d_out, 0, st)) return -1;
     if (!out_dev) COALA_CUDA(cudaMemcpyAsync(out, h->d_out, (size_t)h->cap * 8, cudaMemcpyDeviceToHost, st));
-    COALA_CUDA(cudaMemcpyAsync(h->h_bucket_len, h->d_flags + 1, h->n_domains * sizeof(int), cudaMemcpyDeviceToHost, st));
+    COALA_CUDA(cudaMemcpyAsync(h->h_bucket_len, h->d_flags[0] + 1, h->n_domains * sizeof(int), cudaMemcpyDeviceToHost, st));
     COALA_CUDA(cudaStreamSynchronize(st));
     return 0;
 }

@@ -68,7 +68,7 @@ class SyntheticSharedCSCUVA(object):
             # COALA_SYNTH_COLOR = block (default: id-block stand-in) | graph (the reference's colouring, host mode,
             # ~15 s at 10 M nodes) | graph_gpu (same seeds, GPU mode, ~0.3 s) - SURVEY 8(d) "colour metadata for each
             # graph comes from the colouring with the reference call order"
-            how = os.environ.get("COALA_SYNTH_COLOR", "block")
+            how = self._color_mode(n)
             if how == "block":
                 C = num_colors or max(16, int(0.005 * n))
                 color, topk, score = synth.block_color_meta(n, C)
@@ -78,9 +78,24 @@ class SyntheticSharedCSCUVA(object):
             np.save(os.path.join(self.meta_dir, "topk.npy"), topk)
             np.save(os.path.join(self.meta_dir, "score.npy"), score)
         comm_manager.local_comm.Barrier()
+        self.color_source = {"block": "id-block stand-in (synth.block_color_meta), not derived from the graph",
+                             "graph": "Graph_Coloring host mode on this graph = the reference's colouring (M/graph_coloring.cpp), reference call order",
+                             "graph_gpu": "Graph_Coloring GPU mode on this graph (level-synchronous variant of the reference's colouring, same seeds)"}[self._color_mode(n)]
         self.color_file, self.topk_file, self.score_file = (os.path.join(self.meta_dir, x) for x in ("color.npy", "topk.npy", "score.npy"))
         if verbose and comm_manager.global_rank == 0:
             print("dataset %s ready in %.1fs (features %.1fs)" % (shape, time.time() - t0, t_feat), flush=True)
+
+    @staticmethod
+    def _color_mode(n):
+        """COALA_SYNTH_COLOR = graph (the reference's colouring in host mode: its bits; ~15 s at 10 M nodes, one thread) |
+        graph_gpu (same seeds, GPU mode, ~0.3 s) | block (id-block stand-in).  Default: graph up to 20 M nodes, graph_gpu
+        above ("colour metadata for each graph comes from the colouring with the reference call order")."""
+        how = os.environ.get("COALA_SYNTH_COLOR", "auto")
+        if how == "auto":
+            how = "graph" if n <= 20_000_000 else "graph_gpu"
+        if how not in ("block", "graph", "graph_gpu"):
+            raise ValueError("COALA_SYNTH_COLOR must be auto, block, graph or graph_gpu")
+        return how
 
     def feat_host_array(self):
         """numpy view of the pinned feature table (host side) — used by the CPU baseline only."""
@@ -93,6 +108,14 @@ class SyntheticSharedCSCUVA(object):
         for m in self._segs:
             m.cleanup()
         self._segs = []
+
+    def unlink_segments(self):
+        """Remove the shm names without unmapping (emergency exit while kernels may still read the mappings)."""
+        import ctypes
+        if self.comm.local_rank == 0:
+            libc = ctypes.CDLL(None)
+            for m in self._segs:
+                libc.shm_unlink(m.memory_handle._path)
 
 
 def _copy_npy_into(dst, path, threads=8, chunk_rows=None):

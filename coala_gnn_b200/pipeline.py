@@ -37,6 +37,8 @@ class _Slot(object):
         self.t1 = torch.cuda.Event(enable_timing=True)
         self.used = False
         self.batch = -1
+        self.last_seeds = None   # device tensor the last sample of this slot was drawn from
+        self.meta_used = None    # DevicePipeline: the domain histograms its distribution read
 
 
 class BatchEngine(object):
@@ -81,6 +83,7 @@ class BatchEngine(object):
                 s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 s0.record(ss)
             seeds = seed_fn(slot, ss)
+            slot.last_seeds = seeds
             slot.sampler.sample_async(self.g, seeds, batch_key(self.seed, t, self.rank), ss.cuda_stream)
             if self.record:
                 s1.record(ss)
@@ -123,11 +126,13 @@ class BatchEngine(object):
 
 
 class DevicePipeline(object):
-    """Device-resident form of the path for one cache domain: every rank of the domain runs the
-    (deterministic) GPU distributor on the same inputs and takes its own slice, so there is no seed
-    broadcast; the domain's cache colour histogram is summed with one small NCCL all-reduce every
-    `refresh_counter` batches and stays on the device.  step() returns the rows of batch t (valid on
-    the current stream) while batch t+1 is already in flight."""
+    """Device-resident form of the path for D x L cache domains: every rank runs the (deterministic) GPU
+    distributor on the same inputs - the step's global seed slice and the D domain histograms - and takes
+    its domain's bucket and its own slice of it, so there is no seed broadcast (S/Shared_Tensor.py:102-103).
+    The cache colour histograms never leave the device: every `refresh_counter` batches each rank's counters
+    are all-gathered over NCCL and summed per domain (the reference: gloo all_reduce inside the domain, then
+    all_gather across the domain masters, on CPU tensors, S/Shared_Tensor.py:96-100).  step() returns the rows
+    of batch t (valid on the current stream) while the next batches are already in flight."""
 
     def __init__(self, loader, record_gather_events=False, prefetch=True, seed=None, depth=None):
         self.loader = loader
@@ -137,42 +142,81 @@ class DevicePipeline(object):
         self.g = loader.g
         self.device = loader.device
         assert self.nd._dev_index is not None, "seed list must be device resident"
-        if self.comm.num_master_process != 1:
-            raise NotImplementedError("DevicePipeline drives one cache domain; use the drop-in loader for D > 1")
-        self.B, self.L = self.nd.batch_size, self.comm.local_size
+        self.B, self.L, self.D = self.nd.batch_size, self.comm.local_size, self.comm.num_master_process
         self.engine = BatchEngine(self.g, loader.sampler, self.mgr, self.B, self.device, record_gather_events, depth=depth if prefetch else 1)
         if seed is not None:
             self.engine.seed = int(seed)
-        self.domain_seeds = [torch.zeros(self.B * self.L, dtype=torch.int64, device=self.device) for _ in range(self.engine.nslots)]
-        self.meta = torch.zeros(self.nd.meta_len, dtype=torch.int32, device=self.device)
+        ns = self.engine.nslots
+        if ns + 1 > 8 and self.nd.parsing_method == "node_color":
+            raise ValueError("the distributor has 7 scratch slots for in-flight distributions; prefetch depth must be <= 6")
+        self.domain_seeds = [torch.zeros(self.B * self.L, dtype=torch.int64, device=self.device) for _ in range(ns)]
+        ml = self.nd.meta_len
+        # ring of histogram sets: a refresh writes the next entry and later launches read it, so a distribution
+        # still running on another slot's stream keeps the entry it was launched with (at most `ns` launches are
+        # in flight, hence ns + 2 entries even with refresh_counter = 1)
+        self.meta_ring = [torch.zeros((self.D, ml), dtype=torch.int32, device=self.device) for _ in range(ns + 2)]
+        self.meta_local = [torch.zeros(ml, dtype=torch.int32, device=self.device) for _ in range(ns + 2)]
+        self.meta_world = [torch.zeros((self.comm.global_size, ml), dtype=torch.int32, device=self.device) for _ in range(ns + 2)] \
+            if self.D > 1 else None
+        self.meta_cur = 0
+        doms = self.comm.global_dist_local_rank_list if self.comm.global_size > 1 else [[0]]
+        self._dom_ranks = [torch.tensor(r, dtype=torch.int64, device=self.device) for r in doms]
+        self._dom_blocked = all(list(r) == list(range(d * self.L, (d + 1) * self.L)) for d, r in enumerate(doms))
         self.step_idx = 0
         self.refresh = loader.refresh_counter
         self.prefetch = prefetch
-        n_dist = 1 if self.nd.parsing_method == "node_color" else 0  # D == 1: the pass-through kernel
-        self.kernels_per_step = n_dist + 1 + 7 * len(self.engine.fanouts) + 1  # + set_count, sampler rounds, gather
+        if self.nd.parsing_method != "node_color":
+            n_dist = 0
+        else:
+            n_dist = 1 if self.D == 1 else 3  # pass-through | score + tiled assign + (idle) serial assign
+        self.kernels_per_step = n_dist + 1 + 7 * len(self.engine.fanouts) + 1  # + prologue, sampler rounds, gather
 
     def steps_per_epoch(self):
         return len(self.nd.index_tensor) // self.nd.global_batch_size - 1
 
+    def seed_offset(self, t):
+        return (t % self.steps_per_epoch()) * self.nd.global_batch_size
+
     def _seed_fn(self, t):
         def fn(slot, stream):
-            offset = (t % self.steps_per_epoch()) * self.nd.global_batch_size
+            offset = self.seed_offset(t)
             if t % self.refresh == 0 and t > 0:
                 self.refresh_meta(stream)
+            slot.meta_used = self.meta_ring[self.meta_cur]
             if self.nd.parsing_method == "node_color":
-                dom = self.domain_seeds[t % self.engine.nslots]
-                self.nd.distribute_manager.distribute_async(offset, dom.data_ptr(), [self.meta.data_ptr()], stream.cuda_stream)
+                dom = self.domain_seeds[slot.k]
+                meta = slot.meta_used
+                self.nd.distribute_manager.distribute_async(offset, dom.data_ptr(), [meta[d].data_ptr() for d in range(self.D)],
+                                                            stream.cuda_stream, slot=1 + slot.k)
                 return dom[self.comm.local_rank * self.B:(self.comm.local_rank + 1) * self.B]
-            lo = offset + self.comm.local_rank * self.B
+            lo = offset + self.comm.master_process_index * self.B * self.L + self.comm.local_rank * self.B  # (S/Training_node_distributor.py:41-47)
             return self.nd._dev_index[lo:lo + self.B]
         return fn
 
     def refresh_meta(self, stream):
-        """Colour histogram of the whole domain's cache -> device int32[meta_len] (on `stream`)."""
+        """Colour histograms of every domain's cache -> the next ring entry, int32[D, meta_len] (on `stream`)."""
         cache = self.mgr.COALA_GNN_Cache
-        check(lib().coala_cache_get_cache_data_async(cache._h, self.meta.data_ptr(), self.nd.meta_len, stream.cuda_stream), "get_cache_data")
-        if self.L > 1:
-            dist.all_reduce(self.meta, group=self.comm.nccl_cache_gather)  # runs on the current (= sample) stream
+        nxt = (self.meta_cur + 1) % len(self.meta_ring)
+        local, buf = self.meta_local[nxt], self.meta_ring[nxt]
+        check(lib().coala_cache_get_cache_data_async(cache._h, local.data_ptr(), self.nd.meta_len, stream.cuda_stream), "get_cache_data")
+        if self.D == 1:
+            if self.L > 1:
+                dist.all_reduce(local, group=self.comm.nccl_cache_gather)  # runs on the current (= sample) stream
+            buf[0].copy_(local)
+        else:
+            world = self.meta_world[nxt]
+            dist.all_gather_into_tensor(world, local)  # every rank's counters; NCCL, ordered after `stream`
+            if self._dom_blocked:
+                torch.sum(world.view(self.D, self.L, -1), dim=1, dtype=torch.int32, out=buf)
+            else:
+                for d, ranks in enumerate(self._dom_ranks):
+                    torch.sum(world.index_select(0, ranks), dim=0, dtype=torch.int32, out=buf[d])
+        self.meta_cur = nxt
+
+    @property
+    def meta(self):
+        """The histogram set new launches read (int32[D, meta_len]); D == 1 callers use meta[0]."""
+        return self.meta_ring[self.meta_cur]
 
     def step(self):
         t = self.step_idx

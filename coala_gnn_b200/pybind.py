@@ -129,9 +129,11 @@ class Node_distributor_pybind:
         arr = (C.c_uint64 * len(meta_ptrs))(*[int(p) for p in meta_ptrs])
         check(lib().coala_nd_distribute(self._h, int(offset), int(out_ptr), arr, len(meta_ptrs)), "distribute_node_with_affinity")
 
-    def distribute_async(self, offset, out_dev_ptr, meta_dev_ptrs, stream=0):
+    def distribute_async(self, offset, out_dev_ptr, meta_dev_ptrs, stream=0, slot=1):
+        """Device-resident form: every pointer is a device address.  Distributions that may overlap on different
+        streams must use different scratch slots (1..7; 0 belongs to distribute_node_with_affinity)."""
         arr = (C.c_uint64 * len(meta_dev_ptrs))(*[int(p) for p in meta_dev_ptrs])
-        check(lib().coala_nd_distribute_async(self._h, int(offset), int(out_dev_ptr), arr, len(meta_dev_ptrs), stream),
+        check(lib().coala_nd_distribute_async_slot(self._h, int(offset), int(out_dev_ptr), arr, len(meta_dev_ptrs), int(slot), stream),
               "distribute_async")
 
     def get_num_colors(self):
@@ -194,6 +196,16 @@ class _CacheBase:
 
     def num_sets(self):
         return int(lib().coala_cache_num_sets(self._h))
+
+    def set_num_nodes(self, n):
+        """Row count of the host feature table: ids >= n are refused on the device instead of dereferenced."""
+        check(lib().coala_cache_set_num_nodes(self._h, int(n)), "set_num_nodes")
+
+    def refused_ids(self, reset=True):
+        """Ids refused (out of range) by launches since the last reset; the async gather cannot raise."""
+        n = C.c_uint64()
+        check(lib().coala_cache_refused_ids(self._h, C.byref(n), int(reset)), "refused_ids")
+        return n.value
 
     def export_state(self):
         import numpy as np

@@ -64,6 +64,10 @@ coala_nd* coala_nd_create_plain(uint64_t item_ptr, int n_domains);
 int coala_nd_distribute(coala_nd* h, uint64_t offset, uint64_t out_ptr, const uint64_t* meta_ptrs, int n_meta);
 int coala_nd_distribute_async(coala_nd* h, uint64_t offset, uint64_t out_dev_ptr, const uint64_t* meta_dev_ptrs,
                               int n_meta, void* stream);
+/* same with an explicit scratch slot in [0,8): distributions that may overlap on different streams (one per
+ * in-flight mini-batch of the prefetch engine) must use different slots; slot 0 is the synchronous entry point's */
+int coala_nd_distribute_async_slot(coala_nd* h, uint64_t offset, uint64_t out_dev_ptr, const uint64_t* meta_dev_ptrs,
+                                   int n_meta, int slot, void* stream);
 /* how many int32 entries each cache-meta histogram holds (default num_colors, the size the
  * reference's callers allocate, S/Training_node_distributor.py:33; colour id == num_colors then
  * reads as 0 instead of one past the end). Set num_colors+1 to cover every colour id. */
@@ -120,6 +124,12 @@ int coala_cache_read_feature(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr,
  * captured in a CUDA graph; n is then the upper bound used for sizing. */
 int coala_cache_read_feature_async(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n,
                                    uint64_t n_dev_ptr, void* stream);
+/* Node ids are bounds-checked on the device (the reference dereferences whatever it is given): an id >= the host
+ * table's row count (known from the distributor's colour table, or set here) or >= 2^40 - 1 (the tag's id field) is
+ * refused - its output row is zero-filled and counted.  The synchronous read_feature calls fail when a launch
+ * refused ids; callers of the async form poll coala_cache_refused_ids. */
+int coala_cache_set_num_nodes(coala_cache* c, int64_t num_nodes);
+int coala_cache_refused_ids(coala_cache* c, uint64_t* count, int reset);
 /* same kernel, launched as ONE warp so requests resolve strictly in order (test hook: makes
  * hit/miss counts, tags and colour counters comparable with the sequential oracle) */
 int coala_cache_read_feature_serial(coala_cache* c, uint64_t out_ptr, uint64_t idx_ptr, int64_t n);

@@ -72,6 +72,19 @@ for backend in args.backends.split(","):
         if comm.global_rank == 0:
             print("ok %-8s %-10s %dx%d: %d batches, hit %d miss %d bypass %d" % (backend, distribution, D, Lsz, n_checked, h, m, b), flush=True)
         loader.scheduler.drain()
+        if backend != "nccl":
+            # the device-resident form of the same path (seeds from the GPU distributor, histograms all-gathered on the
+            # device): rows, blocks and this rank's seed list against the oracle's distribution of the same histograms
+            from bench import Checker, check_pipeline
+            from coala_gnn_b200.pipeline import DevicePipeline
+            pipe = DevicePipeline(loader, seed=23)
+            chk = Checker(comm, ds, train, fan, nd, device)
+            check_pipeline(pipe, chk, 3 * args.steps, oracle_batches=3 * args.steps)
+            psum = chk.summary()
+            assert psum["ok"] and psum["seed_lists_checked"] == 3 * args.steps * comm.global_size, psum
+            if comm.global_rank == 0:
+                print("ok %-8s %-10s %dx%d device pipeline: %s" % (backend, distribution, D, Lsz, psum), flush=True)
+            del pipe
         del loader, nd, sampler
         torch.cuda.synchronize()
         dist.barrier()
