@@ -105,7 +105,7 @@ def lib():
         path = _build.LIB
         if _build.needs_build():
             if os.path.exists(_build.NVCC):
-                path = _build.build()
+                path = _build.build()  # re-checks under an inter-process lock
             elif not os.path.exists(path):
                 raise CoalaError("libcoala_b200.so is not built and nvcc is unavailable; there is no CPU fallback")
         L = C.CDLL(path)

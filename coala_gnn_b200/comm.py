@@ -13,7 +13,8 @@ import numpy as np
 import torch
 import torch.distributed as dist
 
-from .pybind import SharedUVAManager, tensor_from_ptr
+from . import binding
+from .pybind import tensor_from_ptr
 
 
 class _Comm:
@@ -152,8 +153,8 @@ class Shared_UVA_Tensor_Manager(object):
         self.comm_manager = comm_manager
         self.tensor_size = int(tensor_size)
         self.device = "cuda:" + str(comm_manager.device_index)
-        self.memory_handle = SharedUVAManager(path, self.tensor_size, comm_manager.node_id, 0, comm_manager.local_comm,
-                                              device=comm_manager.device_index, zero=zero)
+        self.memory_handle = binding.make_shared_uva(path, self.tensor_size, comm_manager.node_id, comm_manager.local_comm,
+                                                     comm_manager.device_index, zero)
         self.device_ptr = self.memory_handle.get_device_ptr()
         self.host_ptr = self.memory_handle.get_host_ptr()
 

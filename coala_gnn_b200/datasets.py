@@ -115,7 +115,8 @@ class SyntheticSharedCSCUVA(object):
         if self.comm.local_rank == 0:
             libc = ctypes.CDLL(None)
             for m in self._segs:
-                libc.shm_unlink(m.memory_handle._path)
+                path = m.memory_handle._path
+                libc.shm_unlink(path if isinstance(path, bytes) else path.encode())
 
 
 def _copy_npy_into(dst, path, threads=8, chunk_rows=None):

@@ -14,7 +14,8 @@ import time
 import torch
 import torch.distributed as dist
 
-from .pybind import NVSHMEM_Manager, SSD_GNN_SSD_Controllers, SSD_GNN_NVSHMEM_Cache, Isolated_Cache, NCCL_SHARD
+from . import binding
+from .pybind import connect_partitioned
 
 
 class COALA_GNN_Manager(object):
@@ -30,8 +31,9 @@ class COALA_GNN_Manager(object):
         self.aggregation_timer = 0.0
         comm = MPI_comm_manager
 
-        self.SSD_Controllers = SSD_GNN_SSD_Controllers(num_ssds, page_size, num_elems, ssd_read_offset, comm.device_index, dim,
-                                                       self.is_simulation)
+        B = binding.mod()  # ctypes classes, or the compiled COALA_GNN_Pybind module (COALA_PYBIND_NATIVE=1): same names
+        self.SSD_Controllers = B.SSD_GNN_SSD_Controllers(num_ssds, page_size, num_elems, ssd_read_offset, comm.device_index, dim,
+                                                         self.is_simulation)
         self.max_sample_size = batch_size
         for i in fan_out:
             self.max_sample_size *= (int(i) + 1)  # (:79-81)
@@ -39,15 +41,16 @@ class COALA_GNN_Manager(object):
         nd = self.node_distributor.distribute_manager
 
         if self.cache_backend == "nvshmem":
-            self.nvshmem_manager = NVSHMEM_Manager(comm.local_comm, comm.local_rank)
-            if comm.local_size > 1:
-                NVSHMEM_Manager.current_group = comm.local_gloo_gather
-            self.COALA_GNN_Cache = SSD_GNN_NVSHMEM_Cache(self.SSD_Controllers, nd, comm.global_rank, comm.local_size, cache_size, sim_ptr)
+            self.nvshmem_manager = B.NVSHMEM_Manager(0 if binding.is_native() else comm.local_comm, comm.local_rank)
+            self.COALA_GNN_Cache = B.SSD_GNN_NVSHMEM_Cache(self.SSD_Controllers, nd, comm.global_rank, comm.local_size, cache_size, sim_ptr,
+                                                           local_slot=comm.local_rank)
+            if comm.local_size > 1:  # every rank of the domain maps every peer's shard (collective)
+                connect_partitioned(self.COALA_GNN_Cache, comm.local_size, comm.local_gloo_gather)
         elif self.cache_backend == "isolated":
-            self.COALA_GNN_Cache = Isolated_Cache(self.SSD_Controllers, nd, comm.global_rank, comm.local_size, cache_size, sim_ptr)
+            self.COALA_GNN_Cache = B.Isolated_Cache(self.SSD_Controllers, nd, comm.global_rank, comm.local_size, cache_size, sim_ptr)
         elif self.cache_backend == "nccl":
-            self.COALA_GNN_Cache = Isolated_Cache(self.SSD_Controllers, nd, comm.global_rank, comm.local_size, cache_size, sim_ptr,
-                                                  kind=NCCL_SHARD)
+            self.COALA_GNN_Cache = B.Isolated_Cache(self.SSD_Controllers, nd, comm.global_rank, comm.local_size, cache_size, sim_ptr,
+                                                    kind=B.NCCL_SHARD)
             G, ms = comm.local_size, self.max_sample_size
             self.nccl_node_tensor = torch.zeros(ms * G, dtype=torch.int64, device=device)
             self.nccl_map_tensor = torch.zeros(ms * G, dtype=torch.int64, device=device)

@@ -1,7 +1,7 @@
 """Mirror of S/Training_node_distributor.py (Node_Distributor) over the GPU distributor."""
 import torch
 
-from .pybind import Node_distributor_pybind
+from . import binding
 
 
 class Node_Distributor(object):
@@ -22,9 +22,9 @@ class Node_Distributor(object):
         if torch.cuda.is_available():
             self._dev_index = self.index_tensor.to("cuda:%d" % comm_manager.device_index)
         item_ptr = self._dev_index.data_ptr() if self._dev_index is not None else self.index_tensor.data_ptr()
-        self.distribute_manager = Node_distributor_pybind(item_ptr, self.comm_manager.node_id, self.batch_size,
-                                                          comm_manager.local_size, comm_manager.num_master_process,
-                                                          color_file, topk_file, score_file, device=comm_manager.device_index)
+        self.distribute_manager = binding.mod().Node_distributor_pybind(item_ptr, self.comm_manager.node_id, self.batch_size,
+                                                                        comm_manager.local_size, comm_manager.num_master_process,
+                                                                        color_file, topk_file, score_file, device=comm_manager.device_index)
         self.num_colors = self.distribute_manager.get_num_colors()
         # one entry per colour id 0..num_colors (the reference sizes these num_colors and reads one past
         # the end for the last colour)

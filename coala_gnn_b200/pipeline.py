@@ -198,7 +198,7 @@ class DevicePipeline(object):
         cache = self.mgr.COALA_GNN_Cache
         nxt = (self.meta_cur + 1) % len(self.meta_ring)
         local, buf = self.meta_local[nxt], self.meta_ring[nxt]
-        check(lib().coala_cache_get_cache_data_async(cache._h, local.data_ptr(), self.nd.meta_len, stream.cuda_stream), "get_cache_data")
+        cache.get_cache_data_async(local.data_ptr(), self.nd.meta_len, stream.cuda_stream)
         if self.D == 1:
             if self.L > 1:
                 dist.all_reduce(local, group=self.comm.nccl_cache_gather)  # runs on the current (= sample) stream

@@ -162,7 +162,7 @@ class Node_distributor_pybind:
 class _CacheBase:
     _kind = ISOLATED
 
-    def __init__(self, controllers, node_distributor, global_rank, n_gpus, cache_size, sim_buf_ptr, kind=None):
+    def __init__(self, controllers, node_distributor, global_rank, n_gpus, cache_size, sim_buf_ptr, kind=None, local_slot=-1):
         self._h = None
         self._ctrl = controllers
         self._nd = node_distributor  # borrowed colour table: the distributor must outlive the cache (M/ssd_gnn_cache.cuh:91)
@@ -170,8 +170,9 @@ class _CacheBase:
         self.local_rank = controllers.cudaDevice
         self.kind = self._kind if kind is None else kind
         nd_h = node_distributor._h if node_distributor is not None else None
+        slot = int(local_slot) if int(local_slot) >= 0 else self._slot()
         self._h = check_handle(lib().coala_cache_create(self.kind, controllers.cudaDevice, controllers.dim, nd_h, int(global_rank),
-                                                        self._slot(), self.num_gpus, int(cache_size), int(sim_buf_ptr)),
+                                                        slot, self.num_gpus, int(cache_size), int(sim_buf_ptr)),
                                type(self).__name__)
 
     def _slot(self):
@@ -182,6 +183,10 @@ class _CacheBase:
             check(lib().coala_cache_get_cache_data(self._h, int(dst_ptr)), "get_cache_data")
         else:
             check(lib().coala_cache_get_cache_data_n(self._h, int(dst_ptr), int(count)), "get_cache_data")
+
+    def get_cache_data_async(self, dst_dev_ptr, count, stream=0):
+        """device-to-device copy of the colour counters on `stream` (they never visit the host)"""
+        check(lib().coala_cache_get_cache_data_async(self._h, int(dst_dev_ptr), int(count), stream), "get_cache_data_async")
 
     def color_counters_dev_ptr(self):
         return int(lib().coala_cache_color_counters_dev_ptr(self._h))
@@ -277,12 +282,10 @@ class SSD_GNN_NVSHMEM_Cache(_CacheBase):
     read_feature runs the single fused gather kernel."""
     _kind = PARTITIONED
 
-    def __init__(self, controllers, node_distributor, global_rank, n_gpus, cache_size, sim_buf_ptr):
-        super().__init__(controllers, node_distributor, global_rank, n_gpus, cache_size, sim_buf_ptr)
+    def __init__(self, controllers, node_distributor, global_rank, n_gpus, cache_size, sim_buf_ptr, local_slot=-1):
+        super().__init__(controllers, node_distributor, global_rank, n_gpus, cache_size, sim_buf_ptr, local_slot=local_slot)
         self._pending = None
         self._peers = []
-        if self.num_gpus > 1 and NVSHMEM_Manager.current_group is not None:
-            self.connect(NVSHMEM_Manager.current_group)
 
     def _slot(self):
         return NVSHMEM_Manager.current_rank if NVSHMEM_Manager.current_rank is not None else self.local_rank
@@ -292,59 +295,23 @@ class SSD_GNN_NVSHMEM_Cache(_CacheBase):
         check(lib().coala_cache_ipc_handle(self._h, buf), "ipc_handle")
         return buf.raw
 
-    _connect_seq = 0
+    def export_fd(self):
+        fd = lib().coala_cache_export_fd(self._h)
+        if fd < 0:
+            raise CoalaError("export_fd: " + lib().coala_last_error().decode())
+        return fd
+
+    def attach_fd(self, peer, fd):
+        check(lib().coala_cache_attach_fd(self._h, int(peer), int(fd)), "attach_fd")
+
+    def attach_ipc(self, peer, handle):
+        check(lib().coala_cache_attach_ipc(self._h, int(peer), handle), "attach_ipc")
+
+    def is_fd_shared(self):
+        return bool(lib().coala_cache_is_fd_shared(self._h))
 
     def connect(self, group):
-        """Collective over the cache domain: every rank maps every peer's shard.  Shards are shared as
-        POSIX file descriptors (VMM allocations) sent over unix sockets; with COALA_CACHE_LEGACY_IPC=1
-        as 64-byte CUDA IPC handles."""
-        import torch.distributed as dist
-        me = dist.get_rank(group)
-        if not lib().coala_cache_is_fd_shared(self._h):
-            handles = [None] * self.num_gpus
-            dist.all_gather_object(handles, self.ipc_handle(), group=group)
-            for r, h in enumerate(handles):
-                if r != me:
-                    check(lib().coala_cache_attach_ipc(self._h, r, h), "attach_ipc")
-            dist.barrier(group=group)
-            return
-        import os
-        import socket
-        SSD_GNN_NVSHMEM_Cache._connect_seq += 1
-        tag = "%s_%d_%d" % (os.environ.get("MASTER_PORT", "0"), dist.get_global_rank(group, 0), SSD_GNN_NVSHMEM_Cache._connect_seq)
-
-        def name(r):  # abstract unix socket: no file system entry, gone when closed
-            return "\0coala_b200_%s_%d" % (tag, r)
-        my_fd = lib().coala_cache_export_fd(self._h)
-        if my_fd < 0:
-            raise CoalaError("export_fd: " + lib().coala_last_error().decode())
-        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-        srv.bind(name(me))
-        srv.listen(self.num_gpus)
-        dist.barrier(group=group)  # every rank is listening
-        conns = {}
-        for r in range(self.num_gpus):
-            if r != me:
-                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
-                c.connect(name(r))  # completes from the listen backlog, no accept needed yet
-                c.sendall(bytes([me]))
-                conns[r] = c
-        served = []
-        for _ in range(self.num_gpus - 1):
-            c, _addr = srv.accept()
-            c.recv(1)
-            socket.send_fds(c, [b"f"], [my_fd])
-            served.append(c)
-        for r, c in conns.items():
-            _msg, fds, _flags, _addr = socket.recv_fds(c, 1, 1)
-            try:
-                check(lib().coala_cache_attach_fd(self._h, r, fds[0]), "attach_fd")
-            finally:
-                os.close(fds[0])
-        dist.barrier(group=group)  # every rank has imported every shard
-        for c in list(conns.values()) + served + [srv]:
-            c.close()
-        os.close(my_fd)
+        connect_partitioned(self, self.num_gpus, group)
 
     def attach_local(self, peer_rank, peer_cache):
         self._peers.append(peer_cache)
@@ -359,6 +326,88 @@ class SSD_GNN_NVSHMEM_Cache(_CacheBase):
         idx_ptr, n = self._pending
         self._pending = None
         check(lib().coala_cache_read_feature(self._h, int(out_ptr), idx_ptr, n), "read_feature")
+
+
+FD_EXCHANGE_TIMEOUT_S = 120.0
+
+
+def connect_partitioned(cache, num_gpus, group):
+    """Collective over the cache domain: every rank maps every peer's shard.  Shards are shared as POSIX file
+    descriptors (VMM allocations) passed over unix sockets (SCM_RIGHTS); with COALA_CACHE_LEGACY_IPC=1 as 64-byte
+    CUDA IPC handles.  `cache` is any binding of the C ABI with is_fd_shared / export_fd / attach_fd / ipc_handle /
+    attach_ipc (the ctypes classes of this file or the compiled COALA_GNN_Pybind module).
+
+    A received descriptor maps the peer's shard read-write, so the exchange is closed to other local processes: each
+    rank listens on a socket inside its own mode-0700 temporary directory (only this uid can reach it), learns its
+    peers' paths and pids over the process group, accepts only connections whose SO_PEERCRED (pid, uid) belongs to a
+    peer of the domain, and every blocking call carries a timeout that names what did not arrive."""
+    import os
+    import shutil
+    import socket
+    import struct
+    import tempfile
+    import torch.distributed as dist
+    me = dist.get_rank(group)
+    if not cache.is_fd_shared():
+        handles = [None] * num_gpus
+        dist.all_gather_object(handles, cache.ipc_handle(), group=group)
+        for r, h in enumerate(handles):
+            if r != me:
+                cache.attach_ipc(r, h)
+        dist.barrier(group=group)
+        return
+    my_fd = cache.export_fd()
+    tmpdir = tempfile.mkdtemp(prefix="coala_b200_fd_")  # mode 0700
+    srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+    conns, served = {}, []
+    try:
+        path = os.path.join(tmpdir, "s")
+        srv.bind(path)
+        srv.listen(num_gpus)
+        srv.settimeout(FD_EXCHANGE_TIMEOUT_S)
+        peers = [None] * num_gpus
+        dist.all_gather_object(peers, (path, os.getpid(), os.getuid()), group=group)  # also: every rank is listening
+        allowed = {(pid, uid) for r, (_p, pid, uid) in enumerate(peers) if r != me}
+        for r in range(num_gpus):
+            if r != me:
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.settimeout(FD_EXCHANGE_TIMEOUT_S)
+                c.connect(peers[r][0])  # completes from the listen backlog, no accept needed yet
+                c.sendall(bytes([me]))
+                conns[r] = c
+        n_served = 0
+        while n_served < num_gpus - 1:
+            try:
+                c, _addr = srv.accept()
+            except socket.timeout:
+                raise CoalaError("shard exchange: rank %d served %d of %d peers within %.0f s" % (me, n_served, num_gpus - 1, FD_EXCHANGE_TIMEOUT_S))
+            c.settimeout(FD_EXCHANGE_TIMEOUT_S)
+            pid, uid, _gid = struct.unpack("3i", c.getsockopt(socket.SOL_SOCKET, socket.SO_PEERCRED, struct.calcsize("3i")))
+            if (pid, uid) not in allowed:
+                c.close()  # not a rank of this cache domain: no descriptor, and it does not use up a slot
+                continue
+            allowed.discard((pid, uid))
+            c.recv(1)
+            socket.send_fds(c, [b"f"], [my_fd])
+            served.append(c)
+            n_served += 1
+        for r, c in conns.items():
+            try:
+                _msg, fds, _flags, _addr = socket.recv_fds(c, 1, 1)
+            except socket.timeout:
+                raise CoalaError("shard exchange: rank %d received nothing from peer %d within %.0f s" % (me, r, FD_EXCHANGE_TIMEOUT_S))
+            if not fds:
+                raise CoalaError("shard exchange: peer %d closed the connection without sending its shard" % r)
+            try:
+                cache.attach_fd(r, fds[0])
+            finally:
+                os.close(fds[0])
+        dist.barrier(group=group)  # every rank has imported every shard
+    finally:
+        for c in list(conns.values()) + served + [srv]:
+            c.close()
+        os.close(my_fd)
+        shutil.rmtree(tmpdir, ignore_errors=True)
 
 
 class NVSHMEM_Manager:

@@ -145,6 +145,8 @@ class MultiLayerNeighborSampler:
             return
         if self._h is not None:
             lib().coala_sampler_destroy(self._h)
+            self._h = None
+        self._views, self._views_for = None, None  # a new native object may reuse the old one's address
         dev = torch.device(g.device)
         dev_index = dev.index if dev.index is not None else torch.cuda.current_device()
         fan = (C.c_int * len(self.fanouts))(*self.fanouts)

@@ -34,9 +34,19 @@ def _dataset(tmp_path, n=20000, e=240000, dim=128):
     return dict(comm=comm, g=g, feat=feat, feat_uva=feat_uva, files=(cf, tf, sf), csc=(indptr, indices, eids), labels=labels, n=n, dim=dim)
 
 
+@pytest.fixture(params=["ctypes", "pybind11"])
+def binding_kind(request):
+    """Every loader test runs over both bindings of the C ABI: the ctypes classes and the compiled pybind11 module
+    (COALA_GNN_Pybind/_native*.so, what a maintainer would build in place of M/COALA_GNN_Pybind.cu)."""
+    from coala_gnn_b200 import binding
+    binding.use_native(request.param == "pybind11")
+    yield request.param
+    binding.use_native(False)
+
+
 @pytest.mark.parametrize("backend", ["isolated", "nvshmem", "nccl"])
 @pytest.mark.parametrize("distribution", ["node_color", "baseline"])
-def test_dataloader_iterates_with_bit_exact_features(tmp_path, backend, distribution):
+def test_dataloader_iterates_with_bit_exact_features(tmp_path, backend, distribution, binding_kind):
     import torch
     from COALA_GNN import Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
     d = _dataset(tmp_path)
