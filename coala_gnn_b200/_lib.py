@@ -59,6 +59,12 @@ SIGNATURES = {
     "coala_cache_set_copy_engine": (_i32, [_vp, _i32]),
     "coala_split_node_list": (_i32, [_u64, _i64, _u64, _u64, _u64, _i32, _i32, _vp]),
     "coala_map_feat_data": (_i32, [_u64, _u64, _u64, _i64, _i32, _vp]),
+    "coala_nccl_unique_id": (_i32, [_vp]),
+    "coala_nccl_version": (_i32, []),
+    "coala_nccl_create": (_vp, [_vp, _i32, _vp, _i32, _i32, _i64, _i32]),
+    "coala_nccl_destroy": (None, [_vp]),
+    "coala_nccl_fetch_async": (_i32, [_vp, _u64, _u64, _i64, _u64, _vp]),
+    "coala_nccl_counters": (_i32, [_vp, _vp, _vp, _vp]),
     "coala_sampler_create": (_vp, [_i32, _u64, _u64, _u64, _i64, _i32, _vp, _i32]),
     "coala_sampler_destroy": (None, [_vp]),
     "coala_sampler_max_sample": (_i64, [_vp]),

@@ -30,37 +30,42 @@ __device__ __forceinline__ int stable_rank_in_block(int g, int G, int (*warp_cnt
     return g >= 0 ? warp_cnt[w][g] + rank : 0;
 }
 
-__global__ void __launch_bounds__(PT) part_count_kernel(const int64_t* __restrict__ idx, int64_t n, int G, int* __restrict__ block_cnt) {
+__global__ void __launch_bounds__(PT) part_count_kernel(const int64_t* __restrict__ idx, int64_t n, const int64_t* __restrict__ n_dev, int G,
+                                                        int* __restrict__ block_cnt) {
     __shared__ int warp_cnt[PT / 32][COALA_MAX_GPUS];
     __shared__ int tot[COALA_MAX_GPUS];
+    if (n_dev) n = min(n, *n_dev);
     const int64_t i = (int64_t)blockIdx.x * PT + threadIdx.x;
     const int g = i < n ? (int)((uint64_t)idx[i] % (uint64_t)G) : -1;
     stable_rank_in_block(g, G, warp_cnt, tot);
     if (threadIdx.x < G) block_cnt[(int64_t)blockIdx.x * G + threadIdx.x] = tot[threadIdx.x];
 }
 
-__global__ void part_scan_kernel(int* __restrict__ block_cnt, int nblocks, int G, int64_t* __restrict__ counter) {
+// counter[g * counter_stride] = size of bucket g (counter_stride > 1: the count is the header word of the bucket itself)
+__global__ void part_scan_kernel(int* __restrict__ block_cnt, int nblocks, int G, int64_t* __restrict__ counter, int64_t counter_stride) {
     const int g = threadIdx.x;
     if (g >= G) return;
     int acc = 0;
     for (int b = 0; b < nblocks; b++) { int x = block_cnt[(int64_t)b * G + g]; block_cnt[(int64_t)b * G + g] = acc; acc += x; }
-    counter[g] = acc;
+    counter[(int64_t)g * counter_stride] = acc;
 }
 
-__global__ void __launch_bounds__(PT) part_scatter_kernel(const int64_t* __restrict__ idx, int64_t n, int G, int max_sample,
-                                                          const int* __restrict__ block_base, int64_t* __restrict__ node,
-                                                          int64_t* __restrict__ map) {
+// bucket g's ids start at node + g * node_stride, its positions at map + g * max_sample
+__global__ void __launch_bounds__(PT) part_scatter_kernel(const int64_t* __restrict__ idx, int64_t n, const int64_t* __restrict__ n_dev, int G,
+                                                          int max_sample, int64_t node_stride, const int* __restrict__ block_base,
+                                                          int64_t* __restrict__ node, int64_t* __restrict__ map) {
     __shared__ int warp_cnt[PT / 32][COALA_MAX_GPUS];
     __shared__ int tot[COALA_MAX_GPUS];
+    if (n_dev) n = min(n, *n_dev);
     const int64_t i = (int64_t)blockIdx.x * PT + threadIdx.x;
     int64_t id = 0;
     int g = -1;
     if (i < n) { id = idx[i]; g = (int)((uint64_t)id % (uint64_t)G); }
     const int r = stable_rank_in_block(g, G, warp_cnt, tot);
     if (g >= 0) {
-        const int64_t slot = (int64_t)max_sample * g + block_base[(int64_t)blockIdx.x * G + g] + r;
-        node[slot] = id;
-        map[slot] = i;
+        const int64_t k = block_base[(int64_t)blockIdx.x * G + g] + r;
+        node[node_stride * g + k] = id;
+        map[(int64_t)max_sample * g + k] = i;
     }
 }
 
@@ -92,12 +97,28 @@ extern "C" int coala_split_node_list(uint64_t idx_ptr, int64_t n, uint64_t node_
     int* block_cnt = nullptr;
     COALA_CUDA(cudaMallocAsync(&block_cnt, (size_t)nblocks * n_gpus * sizeof(int), st));
     const int64_t* idx = reinterpret_cast<const int64_t*>(idx_ptr);
-    part_count_kernel<<<nblocks, PT, 0, st>>>(idx, n, n_gpus, block_cnt);
-    part_scan_kernel<<<1, 32, 0, st>>>(block_cnt, nblocks, n_gpus, counter);
-    part_scatter_kernel<<<nblocks, PT, 0, st>>>(idx, n, n_gpus, max_sample, block_cnt, reinterpret_cast<int64_t*>(node_ptr),
+    part_count_kernel<<<nblocks, PT, 0, st>>>(idx, n, nullptr, n_gpus, block_cnt);
+    part_scan_kernel<<<1, 32, 0, st>>>(block_cnt, nblocks, n_gpus, counter, 1);
+    part_scatter_kernel<<<nblocks, PT, 0, st>>>(idx, n, nullptr, n_gpus, max_sample, max_sample, block_cnt, reinterpret_cast<int64_t*>(node_ptr),
                                                 reinterpret_cast<int64_t*>(map_ptr));
     COALA_CUDA(cudaGetLastError());
     COALA_CUDA(cudaFreeAsync(block_cnt, st));
+    return 0;
+}
+
+// internal form used by the NCCL exchange (nccl_backend.cu): row count on the device, bucket g = [count | ids...] at
+// buckets + g * (1 + max_sample), caller-owned scratch (no allocation on the hot path)
+int coala_partition_buckets(const int64_t* idx, int64_t n_upper, const int64_t* n_dev, int64_t* buckets, int64_t* map, int n_gpus,
+                            int max_sample, int* block_cnt_scratch, cudaStream_t st) {
+    const int nblocks = (int)((n_upper + PT - 1) / PT);
+    if (nblocks == 0) {
+        COALA_CUDA(cudaMemsetAsync(buckets, 0, (size_t)n_gpus * (1 + (size_t)max_sample) * 8, st));
+        return 0;
+    }
+    part_count_kernel<<<nblocks, PT, 0, st>>>(idx, n_upper, n_dev, n_gpus, block_cnt_scratch);
+    part_scan_kernel<<<1, 32, 0, st>>>(block_cnt_scratch, nblocks, n_gpus, buckets, 1 + (int64_t)max_sample);
+    part_scatter_kernel<<<nblocks, PT, 0, st>>>(idx, n_upper, n_dev, n_gpus, max_sample, 1 + (int64_t)max_sample, block_cnt_scratch, buckets + 1, map);
+    COALA_CUDA(cudaGetLastError());
     return 0;
 }
 

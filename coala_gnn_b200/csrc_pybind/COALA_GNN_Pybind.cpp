@@ -116,6 +116,7 @@ struct CacheBase {
         return n;
     }
     uint64_t color_counters_dev_ptr() { return coala_cache_color_counters_dev_ptr(h); }
+    uintptr_t handle() { return reinterpret_cast<uintptr_t>(h); }
     void read_feature_async(uint64_t out, uint64_t idx, int64_t n, uint64_t n_dev_ptr, uintptr_t stream) {
         ck(coala_cache_read_feature_async(h, out, idx, n, n_dev_ptr, as_stream(stream)));
     }
@@ -257,6 +258,7 @@ PYBIND11_MODULE(_native, m) {
     .def("set_num_nodes", &cls::set_num_nodes)                                                                 /* (+) */     \
     .def("refused_ids", &cls::refused_ids, py::arg("reset") = true)                                            /* (+) */     \
     .def("color_counters_dev_ptr", &cls::color_counters_dev_ptr)                                               /* (+) */     \
+    .def("handle", &cls::handle)                                                 /* (+) the C-ABI handle, for coala_nccl_create */ \
     .def("read_feature_async", &cls::read_feature_async, py::arg("out_ptr"), py::arg("idx_ptr"), py::arg("n"),               \
          py::arg("n_dev_ptr") = 0, py::arg("stream") = 0)                                                      /* (+) */     \
     .def_readonly("num_gpus", &cls::num_gpus)

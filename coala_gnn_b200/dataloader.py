@@ -87,8 +87,7 @@ class COALA_GNN_DataLoader(object):
         self.total_count = int(self.index_len / self.node_distributor.global_batch_size) - 1  # (:139-141)
         # fused path: sampler output feeds the gather on the device without a host round trip, and
         # batch t+1 is sampled while batch t is gathered / consumed (pipeline.BatchEngine)
-        self.fused = cache_backend in ("nvshmem", "p2p", "isolated") and hasattr(self.sampler, "sample_async") \
-            and torch.cuda.is_available()
+        self.fused = self.COALA_GNN_Manager.engine_capable and hasattr(self.sampler, "sample_async") and torch.cuda.is_available()
         self.engine = None
         if self.fused:
             from .pipeline import BatchEngine

@@ -9,13 +9,14 @@ Backends (``--cache_backend``):
                   instead of O(G^2) serialized send/recv)
 Output rows land in a persistent double buffer (no per-batch torch.zeros of 151 MB, :138,146).
 """
+import os
 import time
 
 import torch
 import torch.distributed as dist
 
 from . import binding
-from .pybind import connect_partitioned
+from .pybind import connect_partitioned, NcclExchange
 
 
 class COALA_GNN_Manager(object):
@@ -52,9 +53,16 @@ class COALA_GNN_Manager(object):
             self.COALA_GNN_Cache = B.Isolated_Cache(self.SSD_Controllers, nd, comm.global_rank, comm.local_size, cache_size, sim_ptr,
                                                     kind=B.NCCL_SHARD)
             G, ms = comm.local_size, self.max_sample_size
-            self.nccl_node_tensor = torch.zeros(ms * G, dtype=torch.int64, device=device)
-            self.nccl_map_tensor = torch.zeros(ms * G, dtype=torch.int64, device=device)
-            self.nccl_counter_tensor = torch.zeros(G, dtype=torch.int64, device=device)
+            # the exchange as one stream-ordered native call (ncclSend/ncclRecv groups); COALA_NCCL_LEGACY=1 keeps the
+            # reference-shaped host choreography over torch.distributed (split_node_list / nccl_get_feature / map_feat_data)
+            self.nccl_legacy = os.environ.get("COALA_NCCL_LEGACY", "0") == "1"
+            self.nccl = None
+            if self.nccl_legacy:
+                self.nccl_node_tensor = torch.zeros(ms * G, dtype=torch.int64, device=device)
+                self.nccl_map_tensor = torch.zeros(ms * G, dtype=torch.int64, device=device)
+                self.nccl_counter_tensor = torch.zeros(G, dtype=torch.int64, device=device)
+            else:
+                self.nccl = NcclExchange(self.COALA_GNN_Cache, comm.device_index, comm.local_gloo_gather, G, comm.local_rank, ms, dim)
         else:
             raise ValueError(f"Unsupported cache backend: {cache_backend}")
         self._out = [torch.empty((self.max_sample_size, dim), dtype=torch.float32, device=device) for _ in range(2)]
@@ -70,11 +78,24 @@ class COALA_GNN_Manager(object):
         self._flip = (self._flip + 1) % 2
         return self._out[self._flip][:n]
 
+    def gather_async(self, out_ptr, idx_ptr, n_upper, n_dev_ptr, stream):
+        """Enqueue the cached gather of a device-resident id list (length possibly known only on the device) on `stream`:
+        the fused requester-pull kernel (partitioned / isolated), or the NCCL exchange (which blocks once for its counts)."""
+        if self.cache_backend == "nccl" and self.nccl is not None:
+            self.nccl.fetch_async(out_ptr, idx_ptr, n_upper, n_dev_ptr, stream)
+        else:
+            self.COALA_GNN_Cache.read_feature_async(out_ptr, idx_ptr, n_upper, n_dev_ptr, stream)
+
+    @property
+    def engine_capable(self):
+        """Can the prefetch engine drive this backend (everything enqueued on a stream by gather_async)?"""
+        return self.cache_backend in ("nvshmem", "isolated") or (self.cache_backend == "nccl" and self.nccl is not None)
+
     def fetch_feature_async(self, index, n_upper, n_dev_ptr, stream):
-        """Enqueue the gather for a device-resident id list whose length is only known on the device
-        (isolated / partitioned backends). Returns the full-capacity output buffer."""
+        """Enqueue the gather for a device-resident id list whose length is only known on the device.
+        Returns the full-capacity output buffer."""
         out = self._next_out(self.max_sample_size)
-        self.COALA_GNN_Cache.read_feature_async(out.data_ptr(), index, n_upper, n_dev_ptr, stream)
+        self.gather_async(out.data_ptr(), index, n_upper, n_dev_ptr, stream)
         return out
 
     def fetch_feature(self, batch):
@@ -88,6 +109,10 @@ class COALA_GNN_Manager(object):
                 self.COALA_GNN_Cache.read_feature(return_torch.data_ptr(), 0, self.max_sample_size)
             else:
                 self.COALA_GNN_Cache.read_feature(return_torch.data_ptr(), index.data_ptr(), index_size)
+        elif self.nccl is not None:
+            return_torch = self._next_out(index_size)
+            self.nccl.fetch_async(return_torch.data_ptr(), index.data_ptr(), index_size, 0, torch.cuda.current_stream().cuda_stream)
+            torch.cuda.current_stream().synchronize()  # synchronous like the reference's fetch
         else:
             return_torch = self._fetch_nccl(index, index_size)
         self.aggregation_timer += (time.time() - fetch_start)

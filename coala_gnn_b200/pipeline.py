@@ -98,7 +98,7 @@ class BatchEngine(object):
                     self.gather_times.append((slot.t0, slot.t1))
                     slot.t0, slot.t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
                 slot.t0.record(sg)
-            self.mgr.COALA_GNN_Cache.read_feature_async(slot.out.data_ptr(), idx_ptr, self.mgr.max_sample_size, n_ptr, sg.cuda_stream)
+            self.mgr.gather_async(slot.out.data_ptr(), idx_ptr, self.mgr.max_sample_size, n_ptr, sg.cuda_stream)
             if self.record:
                 slot.t1.record(sg)
             slot.ev_gathered.record(sg)

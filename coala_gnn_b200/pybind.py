@@ -14,7 +14,7 @@ from ._lib import lib, check, check_handle, CoalaError
 
 __all__ = [
     "SharedUVAManager", "SSD_GNN_SSD_Controllers", "SSD_GNN_NVSHMEM_Cache", "Isolated_Cache",
-    "Node_distributor_pybind", "NVSHMEM_Manager", "Graph_Coloring", "tensor_from_ptr",
+    "Node_distributor_pybind", "NVSHMEM_Manager", "Graph_Coloring", "tensor_from_ptr", "NcclExchange", "connect_partitioned",
 ]
 
 ISOLATED, PARTITIONED, NCCL_SHARD = 0, 1, 2
@@ -326,6 +326,48 @@ class SSD_GNN_NVSHMEM_Cache(_CacheBase):
         idx_ptr, n = self._pending
         self._pending = None
         check(lib().coala_cache_read_feature(self._h, int(out_ptr), idx_ptr, n), "read_feature")
+
+
+class NcclExchange:
+    """The NCCL all-to-all variant as one stream-ordered call (csrc/nccl_backend.cu; replaces the host choreography of
+    S/COALA_GNN_Manager.py:143-211).  `cache` is this rank's NCCL_SHARD cache (either binding); `group` a process group
+    of the cache domain used once, to ship the 128-byte NCCL id from the domain's first rank."""
+
+    def __init__(self, cache, device, group, n_ranks, rank, max_sample, feat_dim):
+        self._h = None
+        self._cache = cache  # the exchange looks rows up in this shard: keep it alive
+        uid = C.create_string_buffer(128)
+        if n_ranks > 1:
+            import torch.distributed as dist
+            box = [None]
+            if rank == 0:
+                check(lib().coala_nccl_unique_id(uid), "nccl unique id")
+                box[0] = uid.raw
+            dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0), group=group)
+            uid = C.create_string_buffer(box[0], 128)
+        handle = cache._h if hasattr(cache, "_h") else cache.handle()
+        self._h = check_handle(lib().coala_nccl_create(handle, int(device), uid, int(n_ranks), int(rank), int(max_sample), int(feat_dim)),
+                               "NcclExchange")
+
+    def fetch_async(self, out_ptr, idx_ptr, n_upper, n_dev_ptr=0, stream=0):
+        check(lib().coala_nccl_fetch_async(self._h, int(out_ptr), int(idx_ptr), int(n_upper), int(n_dev_ptr), stream), "nccl fetch")
+
+    def counters(self):
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        check(lib().coala_nccl_counters(self._h, C.byref(a), C.byref(b), C.byref(c)))
+        return {"batches": a.value, "rows_served": b.value, "rows_received": c.value}
+
+    @staticmethod
+    def version():
+        return int(lib().coala_nccl_version())
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                lib().coala_nccl_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
 
 
 FD_EXCHANGE_TIMEOUT_S = 120.0

@@ -158,6 +158,23 @@ int coala_split_node_list(uint64_t idx_ptr, int64_t n, uint64_t node_ptr, uint64
 /* map_feat_data (M/ssd_gnn_cache.cuh:327-356, M/cache_kernel.cu:113-137): out[map[r]] = src[r] */
 int coala_map_feat_data(uint64_t out_ptr, uint64_t src_ptr, uint64_t map_ptr, int64_t n, int feat_dim, void* stream);
 
+/* The whole NCCL variant as one stream-ordered call (replaces the host choreography of S/COALA_GNN_Manager.py:143-211:
+ * split_node_list, dist.all_to_all of padded id buckets + all_to_all_single of counts, nccl_get_feature on G streams,
+ * G x G serialised dist.send/recv of rows, map_feat_data per peer).  `shard` is this rank's COALA_CACHE_NCCL_SHARD cache.
+ * The communicator spans the ranks of one cache domain: rank 0 obtains a 128-byte id with coala_nccl_unique_id, the
+ * caller ships it to the other ranks, and every rank calls coala_nccl_create (collective; ncclCommInitRank inside).
+ * NCCL is loaded at run time (the libnccl.so.2 already in the process, or COALA_NCCL_LIB).
+ * coala_nccl_fetch_async: out[i, 0:feat_dim] = feature row of idx[i]; the row count may live on the device (n_dev_ptr,
+ * n_upper then bounds it).  Everything is enqueued on `stream`; the call blocks once, for the 2G bucket counts the row
+ * exchange needs on the host.  Collective: every rank of the domain calls it the same number of times. */
+typedef struct coala_nccl coala_nccl;
+int coala_nccl_unique_id(void* id128);
+int coala_nccl_version(void);
+coala_nccl* coala_nccl_create(coala_cache* shard, int device, const void* id128, int n_ranks, int rank, int64_t max_sample, int feat_dim);
+void coala_nccl_destroy(coala_nccl* x);
+int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t idx_ptr, int64_t n_upper, uint64_t n_dev_ptr, void* stream);
+int coala_nccl_counters(coala_nccl* x, uint64_t* batches, uint64_t* rows_served, uint64_t* rows_received);
+
 /* ------------------------------------------------------------------ stage 2: UVA neighbour sampler
  * replaces dgl MultiLayerNeighborSampler.sample on the UVA CSC graph (call site
  * S/COALA_GNN_DataLoader.py:162; graph arrangement M/shared_UVA.cuh + examples/ssd_gnn_dataloader.py:496-524). */

@@ -76,7 +76,27 @@ def test_dataloader_iterates_with_bit_exact_features(tmp_path, backend, distribu
     loader.print_stats()
 
 
-@pytest.mark.parametrize("backend", ["isolated", "nvshmem"])
+def test_nccl_backend_reference_shaped_choreography(tmp_path, monkeypatch):
+    """COALA_NCCL_LEGACY=1: the exchange driven from Python through the module's own split_node_list / nccl_get_feature /
+    map_feat_data (the call sequence of S/COALA_GNN_Manager.py:143-211) instead of the single native call."""
+    import torch
+    from COALA_GNN import Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
+    monkeypatch.setenv("COALA_NCCL_LEGACY", "1")
+    d = _dataset(tmp_path)
+    B, fan = 128, [5, 5]
+    train = torch.from_numpy(synth.train_ids(d["n"], seed=1))
+    nd = Node_Distributor(d["comm"], train, B, *d["files"], parsing_method="baseline")
+    loader = COALA_GNN_DataLoader(SSD_INFO(1, 512, 1024, 0), nd, d["g"], MultiLayerNeighborSampler(fan, seed=5), B, d["dim"], fan, 2, "cuda:0",
+                                  refresh_counter=3, cache_backend="nccl", sim_buf=d["feat_uva"])
+    assert loader.engine is None and loader.COALA_GNN_Manager.nccl is None
+    for step, (input_nodes, seeds, blocks, feat) in enumerate(loader):
+        inp = input_nodes.cpu().numpy()
+        assert np.array_equal(feat.cpu().numpy().view(np.uint32), d["feat"][inp].view(np.uint32))
+        if step == 5:
+            break
+
+
+@pytest.mark.parametrize("backend", ["isolated", "nvshmem", "nccl"])
 @pytest.mark.parametrize("prefetch", [True, False])
 def test_device_pipeline_two_stream_prefetch_is_bit_exact(tmp_path, backend, prefetch):
     """DevicePipeline (GPU distributor -> sampler -> gather on two streams, batch t+1 in flight while
