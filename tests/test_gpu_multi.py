@@ -44,4 +44,4 @@ def test_one_domain_two_gpus_all_backends():
 def test_two_domains_of_one_gpu_isolated():
     if _n_gpus() < 2:
         pytest.skip("needs 2 GPUs")
-    _run(2, ["--gpus_per_domain", "1", "--backends", "isolated"])
+    _run(2, ["--gpus_per_domain", "1", "--backends", "isolated,nvshmem"])
