@@ -169,7 +169,7 @@ class DevicePipeline(object):
             n_dist = 0
         else:
             n_dist = 1 if self.D == 1 else 3  # pass-through | score + tiled assign + (idle) serial assign
-        self.kernels_per_step = n_dist + 1 + 7 * len(self.engine.fanouts) + 1  # + prologue, sampler rounds, gather
+        self.kernels_per_step = n_dist + 3 * len(self.engine.fanouts) + 1  # + three kernels per sampling round, gather
 
     def steps_per_epoch(self):
         return len(self.nd.index_tensor) // self.nd.global_batch_size - 1

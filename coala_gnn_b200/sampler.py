@@ -167,6 +167,10 @@ class MultiLayerNeighborSampler:
     def max_sample(self):
         return int(lib().coala_sampler_max_sample(self._h))
 
+    def graph_nodes(self):
+        """Nodes of the CUDA graph a sample is launched as (0 before the first sample)."""
+        return int(lib().coala_sampler_graph_nodes(self._h))
+
     def sample_async(self, g, seeds, rng_key=None, stream=0):
         """Enqueue the whole multi-layer sample; results stay in the sampler's device buffers."""
         self._ensure(g, seeds.numel())

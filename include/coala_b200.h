@@ -190,9 +190,11 @@ int64_t coala_sampler_max_sample(coala_sampler* s);
  * and edge ids stay in pinned host memory. */
 int coala_sampler_stage_indptr(coala_sampler* s);
 /* diagnostics (COALA_SAMPLER_TRACE=1 at creation): average milliseconds between consecutive enqueued
- * operations of a sample (seed copy, then per layer: reset, sample_rows, scan, compact, flag, scan,
- * relabel; finally the count read-back).  Returns the number of intervals written. */
+ * operations of a sample (per round: sample_rows, first_occurrence, relabel; finally the count read-back).
+ * Returns the number of intervals written. */
 int coala_sampler_trace(coala_sampler* s, double* avg_ms, int max_n);
+/* nodes of the CUDA graph one sample is launched as (0 before the first sample): 3 kernels per round + the count read-back */
+int coala_sampler_graph_nodes(coala_sampler* s);
 /* enqueue all layers for `ns` seeds (device int64); results stay in the sampler's buffers */
 int coala_sampler_sample_async(coala_sampler* s, uint64_t seeds_dev_ptr, int ns, uint64_t rng_key, void* stream);
 /* after the stream is synchronised: counts[2*L+1] = n_src(l), n_edges(l) for l = 0..L-1 in
