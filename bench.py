@@ -315,8 +315,7 @@ def measure_pipeline(args, comm, loader, device, K, min_seconds, rate_hint, warm
     nw = n_windows_for(comm, rate_hint, K, min_seconds, device)
     torch.cuda.synchronize()
     cache.stats(reset=True)
-    pipe.engine.gather_times.clear()
-    pipe.engine.sample_times.clear()
+    pipe.engine.reset_times()
     ms, region = timed_windows(comm, pipe.step, K, nw, pipe.engine.depth, device, profiler_range)
     h, m, b = cache.stats(reset=True)
     g_ms = pipe.gather_ms()

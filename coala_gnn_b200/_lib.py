@@ -76,6 +76,22 @@ SIGNATURES = {
     "coala_sampler_layer_ptrs": (_i32, [_vp, _i32, _vp, _vp, _vp, _vp]),
     "coala_sampler_input_count_dev_ptr": (_u64, [_vp]),
     "coala_lookup_edge_ids": (_i32, [_u64, _u64, _i64, _u64, _vp]),
+    "coala_batch_key": (_u64, [_u64, _u64, _i32]),
+    "coala_engine_create": (_vp, [_i32, _i32, _i32, _u64, _i32, _i32]),
+    "coala_engine_destroy": (None, [_vp]),
+    "coala_engine_bind_slot": (_i32, [_vp, _i32, _vp, _u64]),
+    "coala_engine_bind_gather": (_i32, [_vp, _vp, _vp, _i64]),
+    "coala_engine_set_seed": (_i32, [_vp, _u64]),
+    "coala_engine_slot_stream": (_u64, [_vp, _i32]),
+    "coala_engine_slot_seeds_dev": (_u64, [_vp, _i32]),
+    "coala_engine_gather_stream": (_u64, [_vp]),
+    "coala_engine_checkpoint": (_i32, [_vp, _vp]),
+    "coala_engine_begin": (_i32, [_vp, _i64, _vp]),
+    "coala_engine_sample_gather": (_i32, [_vp, _i64, _u64, _i32]),
+    "coala_engine_launch_host": (_i32, [_vp, _i64, _u64, _i32, _vp]),
+    "coala_engine_collect": (_i32, [_vp, _i64, _vp, _vp]),
+    "coala_engine_slot_of": (_i32, [_vp, _i64]),
+    "coala_engine_times": (_i32, [_vp, _vp, _vp, _vp, _vp, _i32, _i32]),
     "coala_gc_create": (_vp, [_u64]),
     "coala_gc_destroy": (None, [_vp]),
     "coala_gc_set_adj_csc": (None, [_vp, _u64, _u64]),

@@ -93,6 +93,7 @@ class COALA_GNN_DataLoader(object):
             from .pipeline import BatchEngine
             self.engine = BatchEngine(graph, graph_sampler, self.COALA_GNN_Manager, batch_size, device)
         self._epoch_base = 0  # engine batch index of this epoch's first batch
+        self._launched = 0
         self.copy_blocks = False  # True: every batch owns its id/edge tensors (one clone per array, like DGL)
 
     def __iter__(self):
@@ -102,15 +103,11 @@ class COALA_GNN_DataLoader(object):
         return max(self.total_count, 0)
 
     def _launch(self, i):
-        """Distribute (host scheduler) and enqueue sample + gather of this epoch's batch i."""
+        """Distribute (host scheduler) and enqueue sample + gather of this epoch's batch i: one native call
+        (pinned staging copy of the seeds, H2D, sample graph, gather) - csrc/engine.cu."""
         is_last_iter = i + 1 >= self.total_count  # the scheduler must not start distributing a batch that does not exist
         seeds_cpu = self.scheduler.run(is_last_iter)
-
-        def seed_fn(slot, stream):
-            slot.seeds_pin.copy_(seeds_cpu)
-            slot.seeds.copy_(slot.seeds_pin, non_blocking=True)
-            return slot.seeds
-        self.engine.launch(self._epoch_base + i, seed_fn)
+        self.engine.launch_host(self._epoch_base + i, seeds_cpu.data_ptr(), seeds_cpu.numel())
         self._launched = i + 1
 
     def __next__(self):
@@ -130,17 +127,14 @@ class COALA_GNN_DataLoader(object):
         i = self.counter
         eng = self.engine
         eng.consumer_checkpoint()
-        if getattr(self, "_launched", 0) <= i:
-            self._launch(i)
-        while self._launched <= i + eng.depth and self._launched < self.total_count:
-            self._launch(self._launched)  # prefetch: sampled while batch i is gathered and consumed
+        last = min(i + eng.depth, self.total_count - 1)
+        while self._launched <= last:
+            self._launch(self._launched)  # batch i, then the prefetch: sampled while batch i is gathered and consumed
         self.counter += 1
-        slot = eng.slot_of(self._epoch_base + i)
-        torch.cuda.current_stream().wait_event(slot.ev_sampled)
         # views into the slot's buffers: valid until `engine.depth` more batches have been drawn (the slot is then resampled)
-        input_nodes, output_nodes, blocks = slot.sampler.collect(copy=self.copy_blocks)
-        eng.wait(self._epoch_base + i)
-        return input_nodes, output_nodes, blocks, slot.out[:input_nodes.numel()]
+        slot, counts = eng.collect(self._epoch_base + i)
+        input_nodes, output_nodes, blocks = slot.sampler.blocks_from_counts(counts, copy=self.copy_blocks)
+        return input_nodes, output_nodes, blocks, slot.out[:counts[0]]
 
     def print_stats(self):
         self.COALA_GNN_Manager.print_stats()

@@ -86,6 +86,15 @@ class COALA_GNN_Manager(object):
         else:
             self.COALA_GNN_Cache.read_feature_async(out_ptr, idx_ptr, n_upper, n_dev_ptr, stream)
 
+    def native_handles(self):
+        """(coala_cache*, coala_nccl* | None) as integers, for the native batch engine (either binding)."""
+        c = self.COALA_GNN_Cache
+        ch = c._h if hasattr(c, "_h") else c.handle()
+        nh = None
+        if self.cache_backend == "nccl" and self.nccl is not None:
+            nh = self.nccl._h
+        return ch, nh
+
     @property
     def engine_capable(self):
         """Can the prefetch engine drive this backend (everything enqueued on a stream by gather_async)?"""

@@ -15,94 +15,106 @@ a slot is rewritten only after its previous gather finished and the consumer mov
 `BatchEngine` is shared by the drop-in iterator (`COALA_GNN_DataLoader`, seeds come from the host
 scheduler) and by `DevicePipeline` (seeds come from the GPU distributor, no host data at all).
 """
+import ctypes as C
+
 import torch
 import torch.distributed as dist
 
-from ._lib import lib, check
-from .sampler import MultiLayerNeighborSampler, batch_key
+from ._lib import lib, check, check_handle
+from .pybind import tensor_from_ptr
+from .sampler import MultiLayerNeighborSampler, batch_key  # noqa: F401  (batch_key re-exported for callers)
 
 
 class _Slot(object):
-    def __init__(self, k, fanouts, batch_size, out, device, hbm_indptr=None):
+    """Python face of one native engine slot: its sampler object, output rows, stream and seed staging buffer."""
+
+    def __init__(self, k, fanouts, graph, batch_size, out, device, hbm_indptr=None):
         self.k = k
         self.sampler = MultiLayerNeighborSampler(fanouts, hbm_indptr=hbm_indptr)
-        self.seeds = torch.zeros(batch_size, dtype=torch.int64, device=device)
-        self.seeds_pin = torch.zeros(batch_size, dtype=torch.int64).pin_memory()
+        self.sampler._ensure(graph, batch_size)
+        self.sampler._last_g = graph
         self.out = out
-        # sampling kernels are small and latency bound: high priority so that they take SM slots as gather CTAs retire
-        self.stream = torch.cuda.Stream(device=device, priority=-1)
-        self.ev_sampled = torch.cuda.Event()
-        self.ev_gathered = torch.cuda.Event()
-        self.t0 = torch.cuda.Event(enable_timing=True)
-        self.t1 = torch.cuda.Event(enable_timing=True)
-        self.used = False
+        self.device = device
+        self.stream = None       # torch view of the slot's native stream (distribution / refresh are enqueued there)
+        self.seeds = None        # device int64[batch_size] staging buffer (host seed lists land here)
         self.batch = -1
-        self.last_seeds = None   # device tensor the last sample of this slot was drawn from
+        self._last = (0, 0)      # (device pointer, count) of the seed list the last sample of this slot was drawn from
         self.meta_used = None    # DevicePipeline: the domain histograms its distribution read
+
+    @property
+    def last_seeds(self):
+        return tensor_from_ptr(self._last[0], (self._last[1],), torch.int64, self.device)
 
 
 class BatchEngine(object):
-    """launch(t, seed_fn) enqueues batch t; wait(t) makes the current stream wait for its rows.
-    `depth` batches can be in flight behind the one being consumed (depth + 1 slots).  Each slot samples on
-    its own stream: a sample is a dependent chain of small kernels and host round trips that leaves the GPU
-    and the host link mostly idle, so two of them overlap almost perfectly; gathers run in batch order on
-    one stream.  Measured at igb-small N=1 (sampler-bound): depth 1 / 2 / 3 = 7.7 K / 11.3 K / 13.4 K batches/s."""
+    """launch*(t, ...) enqueues batch t; collect(t) / wait(t) make the current stream wait for it.  `depth` batches can be
+    in flight behind the one being consumed (depth + 1 slots).  Each slot samples on its own stream: a sample is a dependent
+    chain of small kernels and host round trips that leaves the GPU and the host link mostly idle, so several of them overlap
+    almost perfectly; gathers run in batch order on one stream.  Measured at igb-small N=1 (sampler-bound): depth 1 / 2 / 3 =
+    7.7 K / 11.3 K / 13.4 K batches/s.  The enqueue sequence itself is native (csrc/engine.cu): one C call per batch."""
 
     def __init__(self, graph, sampler, manager, batch_size, device, record_gather_events=False, depth=None):
         self.g, self.mgr, self.device = graph, manager, device
-        self.seed, self.rank = sampler.seed, sampler.rank
+        self._seed, self.rank = int(sampler.seed), int(sampler.rank)
         self.fanouts = list(sampler.fanouts)
+        self.batch_size = int(batch_size)
         import os
         if depth is None:
             depth = int(os.environ.get("COALA_PREFETCH_DEPTH", "3"))
         self.depth = max(1, int(depth))
         self.nslots = self.depth + 1
-        self.s_gather = torch.cuda.Stream(device=device)
-        self.ev_consumed = torch.cuda.Event()
+        dev_index = torch.device(device).index
+        if dev_index is None:
+            dev_index = torch.cuda.current_device()
+        self._lib = lib()
+        self._h = check_handle(self._lib.coala_engine_create(dev_index, self.nslots, self.batch_size, self._seed & ((1 << 64) - 1), self.rank,
+                                                             1 if record_gather_events else 0), "engine")
         outs = manager.out_buffers(self.nslots)
-        self.slots = [_Slot(k, self.fanouts, batch_size, outs[k], device, getattr(sampler, "hbm_indptr", None)) for k in range(self.nslots)]
+        self.slots = [_Slot(k, self.fanouts, graph, batch_size, outs[k], device, getattr(sampler, "hbm_indptr", None)) for k in range(self.nslots)]
         for s in self.slots:
-            s.sampler._ensure(graph, batch_size)
+            check(self._lib.coala_engine_bind_slot(self._h, s.k, s.sampler._h, s.out.data_ptr()), "engine slot")
+            s.stream = torch.cuda.ExternalStream(int(self._lib.coala_engine_slot_stream(self._h, s.k)), device=device)
+            s.seeds = tensor_from_ptr(int(self._lib.coala_engine_slot_seeds_dev(self._h, s.k)), (self.batch_size,), torch.int64, device, owner=self)
+        cache_h, nccl_h = manager.native_handles()
+        check(self._lib.coala_engine_bind_gather(self._h, cache_h, nccl_h, manager.max_sample_size), "engine gather")
+        self.s_gather = torch.cuda.ExternalStream(int(self._lib.coala_engine_gather_stream(self._h)), device=device)
         self.record = record_gather_events
-        self.gather_times = []  # (start, end) event pairs of finished launches
-        self.sample_times = []  # same for distribution + sampling (the other stream)
         self.launched = 0
+        self._counts = (C.c_int64 * (2 * len(self.fanouts) + 1))()
+        self._NOCP = C.c_void_p((1 << 64) - 1)
+
+    @property
+    def seed(self):
+        return self._seed
+
+    @seed.setter
+    def seed(self, v):
+        self._seed = int(v)
+        check(self._lib.coala_engine_set_seed(self._h, self._seed & ((1 << 64) - 1)))
 
     def consumer_checkpoint(self):
         """Everything the consumer enqueued so far on the current stream precedes any slot reuse."""
-        self.ev_consumed.record(torch.cuda.current_stream())
+        check(self._lib.coala_engine_checkpoint(self._h, torch.cuda.current_stream().cuda_stream), "engine checkpoint")
+
+    def launch_host(self, t, seeds_host_ptr, n):
+        """Batch t from a host seed list (the drop-in iterator): pinned staging + H2D + sample + gather, one native call."""
+        check(self._lib.coala_engine_launch_host(self._h, t, seeds_host_ptr, n, self._NOCP), "engine launch")
+        slot = self.slots[t % self.nslots]
+        slot.batch, slot._last = t, (slot.seeds.data_ptr(), n)
+        self.launched = t + 1
+        return slot
 
     def launch(self, t, seed_fn):
-        slot = self.slots[t % self.nslots]
-        ss, sg = slot.stream, self.s_gather
-        ss.wait_event(self.ev_consumed)
-        if slot.used:
-            ss.wait_event(slot.ev_gathered)  # the previous gather of this slot read the sampler's id list
-        with torch.cuda.stream(ss):
-            if self.record:
-                s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                s0.record(ss)
-            seeds = seed_fn(slot, ss)
-            slot.last_seeds = seeds
-            slot.sampler.sample_async(self.g, seeds, batch_key(self.seed, t, self.rank), ss.cuda_stream)
-            if self.record:
-                s1.record(ss)
-                self.sample_times.append((s0, s1))
-            slot.ev_sampled.record(ss)
-        sg.wait_event(slot.ev_sampled)
-        sg.wait_event(self.ev_consumed)      # the rows of the batch that used this buffer before are no longer needed
-        idx_ptr, n_ptr = slot.sampler.input_nodes_dev_ptrs()
-        with torch.cuda.stream(sg):
-            if self.record:
-                if slot.used:
-                    self.gather_times.append((slot.t0, slot.t1))
-                    slot.t0, slot.t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                slot.t0.record(sg)
-            self.mgr.gather_async(slot.out.data_ptr(), idx_ptr, self.mgr.max_sample_size, n_ptr, sg.cuda_stream)
-            if self.record:
-                slot.t1.record(sg)
-            slot.ev_gathered.record(sg)
-        slot.used, slot.batch = True, t
+        """Batch t from a device-resident seed list: seed_fn(slot, slot.stream) enqueues whatever produces the seeds on the slot's
+        stream (the GPU distributor, a histogram refresh) and returns (device pointer, count) or an int64 device tensor."""
+        k = self._lib.coala_engine_begin(self._h, t, self._NOCP)
+        if k < 0:
+            check(-1, "engine begin")
+        slot = self.slots[k]
+        seeds = seed_fn(slot, slot.stream)
+        ptr, n = seeds if isinstance(seeds, tuple) else (seeds.data_ptr(), seeds.numel())
+        check(self._lib.coala_engine_sample_gather(self._h, t, ptr, n), "engine sample/gather")
+        slot.batch, slot._last = t, (ptr, n)
         self.launched = t + 1
         return slot
 
@@ -112,17 +124,40 @@ class BatchEngine(object):
         return slot
 
     def wait(self, t):
-        slot = self.slot_of(t)
-        torch.cuda.current_stream().wait_event(slot.ev_gathered)
-        return slot
+        """The current stream waits for the rows of batch t (no host wait)."""
+        check(self._lib.coala_engine_collect(self._h, t, None, torch.cuda.current_stream().cuda_stream), "engine wait")
+        return self.slots[t % self.nslots]
+
+    def collect(self, t):
+        """The current stream waits for blocks and rows of batch t; the host waits for the block sizes. Returns (slot, counts)."""
+        check(self._lib.coala_engine_collect(self._h, t, self._counts, torch.cuda.current_stream().cuda_stream), "engine collect")
+        return self.slots[t % self.nslots], self._counts
+
+    def _times(self, reset=False):
+        g, s, ng, ns = C.c_double(), C.c_double(), C.c_uint64(), C.c_uint64()
+        check(self._lib.coala_engine_times(self._h, C.byref(g), C.byref(ng), C.byref(s), C.byref(ns), 1, 1 if reset else 0), "engine times")
+        return g.value, ng.value, s.value, ns.value
+
+    def reset_times(self):
+        torch.cuda.synchronize()
+        self._times(reset=True)
 
     def gather_ms(self):
-        torch.cuda.synchronize()
-        return [a.elapsed_time(b) for a, b in self.gather_times]
+        """[mean CUDA-event time of the gather launches since reset_times()] (empty when nothing was recorded)."""
+        g, ng, _, _ = self._times()
+        return [g] if ng else []
 
     def sample_ms(self):
-        torch.cuda.synchronize()
-        return [a.elapsed_time(b) for a, b in self.sample_times]
+        _, _, s, ns = self._times()
+        return [s] if ns else []
+
+    def __del__(self):
+        try:
+            if getattr(self, "_h", None):
+                self._lib.coala_engine_destroy(self._h)
+                self._h = None
+        except Exception:
+            pass
 
 
 class DevicePipeline(object):
@@ -159,6 +194,8 @@ class DevicePipeline(object):
         self.meta_world = [torch.zeros((self.comm.global_size, ml), dtype=torch.int32, device=self.device) for _ in range(ns + 2)] \
             if self.D > 1 else None
         self.meta_cur = 0
+        self._meta_ptrs = [[m[d].data_ptr() for d in range(self.D)] for m in self.meta_ring]
+        self._dev_index_ptr = self.nd._dev_index.data_ptr()
         doms = self.comm.global_dist_local_rank_list if self.comm.global_size > 1 else [[0]]
         self._dom_ranks = [torch.tensor(r, dtype=torch.int64, device=self.device) for r in doms]
         self._dom_blocked = all(list(r) == list(range(d * self.L, (d + 1) * self.L)) for d, r in enumerate(doms))
@@ -181,16 +218,15 @@ class DevicePipeline(object):
         def fn(slot, stream):
             offset = self.seed_offset(t)
             if t % self.refresh == 0 and t > 0:
-                self.refresh_meta(stream)
+                with torch.cuda.stream(stream):  # torch ops (NCCL, reductions) of the refresh go to the slot's stream
+                    self.refresh_meta(stream)
             slot.meta_used = self.meta_ring[self.meta_cur]
             if self.nd.parsing_method == "node_color":
                 dom = self.domain_seeds[slot.k]
-                meta = slot.meta_used
-                self.nd.distribute_manager.distribute_async(offset, dom.data_ptr(), [meta[d].data_ptr() for d in range(self.D)],
-                                                            stream.cuda_stream, slot=1 + slot.k)
-                return dom[self.comm.local_rank * self.B:(self.comm.local_rank + 1) * self.B]
+                self.nd.distribute_manager.distribute_async(offset, dom.data_ptr(), self._meta_ptrs[self.meta_cur], stream.cuda_stream, slot=1 + slot.k)
+                return dom.data_ptr() + 8 * self.comm.local_rank * self.B, self.B
             lo = offset + self.comm.master_process_index * self.B * self.L + self.comm.local_rank * self.B  # (S/Training_node_distributor.py:41-47)
-            return self.nd._dev_index[lo:lo + self.B]
+            return self._dev_index_ptr + 8 * lo, self.B
         return fn
 
     def refresh_meta(self, stream):
@@ -240,3 +276,9 @@ class DevicePipeline(object):
 
     def gather_ms(self):
         return self.engine.gather_ms()
+
+    def __del__(self):
+        try:
+            torch.cuda.synchronize()
+        except Exception:
+            pass

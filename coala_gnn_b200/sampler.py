@@ -79,18 +79,54 @@ class Block:
     """One bipartite layer: edges (edge_src[e] -> edge_dst[e]) in local ids; dst nodes are the first
     ``num_dst_nodes`` src nodes. srcdata['_ID'] / dstdata['_ID'] are the global node ids (dgl.NID).
     ``edge_pos`` are the CSC positions of the sampled edges; ``edge_id`` / edata['_ID'] (the graph's
-    edge ids at those positions) are fetched from the UVA edge-id array on first use."""
+    edge ids at those positions) are fetched from the UVA edge-id array on first use.
+    The id / edge tensors are views of the sampler's device buffers cut on first access (the iterator hands out
+    a batch per 0.1 ms: a training loop pays for the views it touches, not for eight slices per batch)."""
 
-    def __init__(self, graph, src_nodes, n_dst, edge_src, edge_dst, edge_pos):
-        self._g = graph
-        self.src_nodes, self.dst_nodes = src_nodes, src_nodes[:n_dst]
-        self.edge_src, self.edge_dst, self.edge_pos = edge_src, edge_dst, edge_pos
-        self._edge_id = None
-        self.srcdata = _Frame(graph, self.src_nodes)
-        self.dstdata = _Frame(graph, self.dst_nodes)
-        self.srcdata["_ID"] = self.src_nodes
-        self.dstdata["_ID"] = self.dst_nodes
-        self.edata = _EdgeFrame(self)
+    __slots__ = ("_g", "_v", "_n_src", "_n_dst", "_ne", "_t", "_edge_id", "_srcdata", "_dstdata", "_edata")
+
+    def __init__(self, graph, views, n_src, n_dst, n_edges, copy=False):
+        self._g, self._v = graph, views
+        self._n_src, self._n_dst, self._ne = int(n_src), int(n_dst), int(n_edges)
+        self._t = [None, None, None, None]
+        self._edge_id = self._srcdata = self._dstdata = self._edata = None
+        if copy:  # the batch owns its arrays (a later sample with the same sampler object overwrites the buffers)
+            self._t = [views[0][:self._n_src].clone()] + [views[j][:self._ne].clone() for j in (1, 2, 3)]
+
+    def _view(self, j):
+        t = self._t[j]
+        if t is None:
+            t = self._t[j] = self._v[j][:self._n_src if j == 0 else self._ne]
+        return t
+
+    src_nodes = property(lambda self: self._view(0))
+    edge_src = property(lambda self: self._view(1))
+    edge_dst = property(lambda self: self._view(2))
+    edge_pos = property(lambda self: self._view(3))
+
+    @property
+    def dst_nodes(self):
+        return self._view(0)[:self._n_dst]
+
+    @property
+    def srcdata(self):
+        if self._srcdata is None:
+            self._srcdata = _Frame(self._g, self.src_nodes)
+            self._srcdata["_ID"] = self.src_nodes
+        return self._srcdata
+
+    @property
+    def dstdata(self):
+        if self._dstdata is None:
+            self._dstdata = _Frame(self._g, self.dst_nodes)
+            self._dstdata["_ID"] = self.dst_nodes
+        return self._dstdata
+
+    @property
+    def edata(self):
+        if self._edata is None:
+            self._edata = _EdgeFrame(self)
+        return self._edata
 
     @property
     def edge_id(self):
@@ -107,15 +143,15 @@ class Block:
         return self._edge_id
 
     def number_of_src_nodes(self):
-        return int(self.src_nodes.numel())
+        return self._n_src
 
     def number_of_dst_nodes(self):
-        return int(self.dst_nodes.numel())
+        return self._n_dst
 
     num_src_nodes, num_dst_nodes = number_of_src_nodes, number_of_dst_nodes
 
     def num_edges(self):
-        return int(self.edge_src.numel())
+        return self._ne
 
     def edges(self):
         return self.edge_src, self.edge_dst
@@ -206,22 +242,21 @@ class MultiLayerNeighborSampler:
     def collect(self, copy=True):
         """Wait for the last sample_async and wrap the buffers. copy=False returns views that a later
         sample with this sampler object overwrites."""
-        L = len(self.fanouts)
-        counts = (C.c_int64 * (2 * L + 1))()
+        counts = (C.c_int64 * (2 * len(self.fanouts) + 1))()
         check(lib().coala_sampler_counts(self._h, counts), "sampler counts")
+        return self.blocks_from_counts(counts, copy)
+
+    def blocks_from_counts(self, counts, copy=False):
+        """(input_nodes, output_nodes, blocks) of the finished sample whose sizes are `counts` (coala_sampler_counts order)."""
+        L = len(self.fanouts)
         if getattr(self, "_views_for", None) != self._h:
             self._wrap_buffers()
             self._views_for = self._h
         g = self._last_g
         blocks = []
         for k in range(L):
-            n_src, ne = counts[2 * k], counts[2 * k + 1]
             n_dst = counts[2 * (k + 1)] if k + 1 < L else counts[2 * L]
-            v = self._views[k]
-            ts = [v[0][:n_src], v[1][:ne], v[2][:ne], v[3][:ne]]
-            if copy:
-                ts = [t.clone() for t in ts]
-            blocks.append(Block(g, ts[0], n_dst, ts[1], ts[2], ts[3]))
+            blocks.append(Block(g, self._views[k], counts[2 * k], n_dst, counts[2 * k + 1], copy))
         return blocks[0].src_nodes, blocks[-1].dst_nodes, blocks
 
     def sample(self, g, seeds, rng_key=None):

@@ -211,6 +211,40 @@ int coala_sampler_layer_ptrs(coala_sampler* s, int layer, uint64_t* src_nodes, u
 int coala_lookup_edge_ids(uint64_t edge_ids_ptr, uint64_t pos_dev_ptr, int64_t n, uint64_t out_dev_ptr, void* stream);
 uint64_t coala_sampler_input_count_dev_ptr(coala_sampler* s); /* device int64: n input nodes */
 
+/* ------------------------------------------------------------------ the iterator's per-batch enqueue sequence
+ * replaces the body of COALA_GNN_DataLoader.__next__ (S/COALA_GNN_DataLoader.py:149-167: scheduler.run -> seeds .to(device)
+ * -> sampler.sample -> fetch_feature, serial per batch) with one call per batch that enqueues seeds H2D + sample on a
+ * slot stream and the cached gather on the gather stream; n_slots batches rotate (n_slots - 1 in flight behind the one
+ * being consumed).  The batch's RNG key is coala_batch_key(seed, t, rank) (same arithmetic as oracle.batch_key). */
+typedef struct coala_engine coala_engine;
+uint64_t coala_batch_key(uint64_t seed, uint64_t batch_idx, int rank);
+coala_engine* coala_engine_create(int device, int n_slots, int batch_size, uint64_t seed, int rank, int record_times);
+void coala_engine_destroy(coala_engine* e);
+/* slot k samples with `sampler` and gathers into out_ptr (device fp32[max_sample, feat_dim], caller-owned) */
+int coala_engine_bind_slot(coala_engine* e, int k, coala_sampler* sampler, uint64_t out_ptr);
+/* the gather of every slot: the fused cache kernel (nccl == NULL) or the NCCL exchange over its shard */
+int coala_engine_bind_gather(coala_engine* e, coala_cache* cache, coala_nccl* nccl, int64_t max_sample);
+int coala_engine_set_seed(coala_engine* e, uint64_t seed);
+uint64_t coala_engine_slot_stream(coala_engine* e, int k);    /* cudaStream_t of slot k (distribution / refresh go here) */
+uint64_t coala_engine_slot_seeds_dev(coala_engine* e, int k); /* device int64[batch_size] staging buffer of slot k */
+uint64_t coala_engine_gather_stream(coala_engine* e);
+/* everything the consumer enqueued so far on `consumer_stream` precedes any later slot reuse */
+int coala_engine_checkpoint(coala_engine* e, void* consumer_stream);
+/* two-step launch (device-resident seeds): begin returns the slot index (-1 on failure) after ordering the slot's stream;
+ * the caller may enqueue the seed distribution on that stream; sample_gather then enqueues sample + gather.
+ * consumer_stream == (void*)~0: no checkpoint (the caller made one for this step already). */
+int coala_engine_begin(coala_engine* e, int64_t t, void* consumer_stream);
+int coala_engine_sample_gather(coala_engine* e, int64_t t, uint64_t seeds_dev_ptr, int n_seeds);
+/* one-step launch from a HOST seed list (the drop-in iterator): pinned staging copy + H2D + sample + gather */
+int coala_engine_launch_host(coala_engine* e, int64_t t, uint64_t seeds_host_ptr, int n_seeds, void* consumer_stream);
+/* consumer_stream waits for batch t's rows; with counts != NULL the host also waits for the block sizes
+ * (counts[2L+1] as coala_sampler_counts) and the stream for the blocks */
+int coala_engine_collect(coala_engine* e, int64_t t, int64_t* counts, void* consumer_stream);
+int coala_engine_slot_of(coala_engine* e, int64_t t); /* slot holding batch t, -1 if it is not in flight */
+/* record_times != 0: mean CUDA-event time of the gather launches and of the sample-stream work (distribution + sampling) */
+int coala_engine_times(coala_engine* e, double* gather_ms_mean, uint64_t* n_gather, double* sample_ms_mean, uint64_t* n_sample,
+                       int sync, int reset);
+
 /* ------------------------------------------------------------------ offline colour metadata
  * replaces Graph_Coloring (M/graph_coloring.h:15-68, M/graph_coloring.cpp; bound at
  * M/COALA_GNN_Pybind.cu:65-77). Host code, as in the reference. */

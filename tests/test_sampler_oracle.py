@@ -79,3 +79,12 @@ def test_multilayer_matches_fast_path_and_shapes():
         assert np.array_equal(b["src_nodes"][b["edge_src"]], indices[pos])
     inp2, tot = oracle.sample_blocks_fast(indptr, indices, seeds, [10, 5, 5], bkey, 256 * 11 * 6 * 6)
     assert np.array_equal(inp, inp2) and tot == sum(len(b["edge_src"]) for b in blocks)
+
+
+def test_native_batch_key_matches_oracle_and_python():
+    """The native batch engine derives a batch's RNG key itself (csrc/engine.cu): same arithmetic as oracle.batch_key."""
+    from coala_gnn_b200._lib import lib
+    from coala_gnn_b200.sampler import batch_key
+    for seed, t, rank in [(1, 0, 0), (11, 5, 3), (2 ** 63 + 5, 123456789, 7), (77, 2 ** 40, 15), (1001, 999999, 1)]:
+        k = lib().coala_batch_key(seed & (2 ** 64 - 1), t, rank)
+        assert k == batch_key(seed, t, rank) == oracle.batch_key(seed, t, rank)
