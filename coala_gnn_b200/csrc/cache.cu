@@ -60,12 +60,11 @@ struct coala_cache {
     VmmRegion peer_region[COALA_MAX_GPUS];
     int copy_engine = 0;   // 0 = registers, 1 = bulk asynchronous copies (coala_cache_set_copy_engine / COALA_GATHER_ENGINE)
     int bulk_nbuf = 3;     // row buffers per warp of engine 1 (COALA_GATHER_NBUF = 2|3)
-    int bulk_waves = 2;    // COALA_GATHER_BULK_WAVES
-    int waves = 2;
-    int ctas_per_sm = 2;   // residency cap of the gather (see launch_gather)
+    int ctas_per_sm = 2;   // resident CTAs per SM of the gather's single wave (see launch_gather)
     size_t smem_per_sm = 228 * 1024;
-    int min_blocks = 3;  // __launch_bounds__ variant of the gather kernel (resident CTAs per SM)
-    int sm_count = 148, blocks_per_sm = 4;
+    int sm_count = 148;
+    GatherWork* d_work = nullptr;  // rotating pool of device-side work counters (one per in-flight launch)
+    unsigned launch_seq = 0;
     std::vector<int32_t> h_counters;
 };
 
@@ -78,44 +77,42 @@ extern "C" int coala_cache_dim_for(int dim) {
     return -1;  // "Only Feature Embedding Size less than 8KB is supported" (M/ssd_gnn_cache.cuh:43-44)
 }
 
-template <int VPL, bool SYS, int MINB>
+constexpr int GATHER_WORK_POOL = 8;  // launches of one cache object that may be in flight at once (different streams)
+
+static GatherWork* next_work(coala_cache* c) { return c->d_work + (c->launch_seq++ % GATHER_WORK_POOL); }
+
+// One resident wave: `ctas_per_sm` CTAs of 8 warps per SM pull chunks of rows from a device-side counter (cache.cuh) until
+// the list - whose length may only be known on the device - is exhausted.
+//
+// SM budget: the gather is bandwidth bound and saturates its link with 16 warps per SM, while the next batch's sampling
+// kernels (other streams, higher priority) are latency bound and need resident warps to keep host round trips in flight.
+// The residency cap is enforced by reserving (unused) dynamic shared memory, so registers and warp slots stay free for the
+// sampler, and because the wave is resident from the start the sampler's CTAs never displace part of a gather (with the
+// earlier two-wave grid the second wave queued behind them).  COALA_GATHER_CTAS_PER_SM overrides (1..3).
+template <int VPL, bool SYS>
 static int launch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
                          bool serial) {
     if (n <= 0) return 0;
     if (serial) {
-        coala_gather_kernel<VPL, SYS, MINB><<<1, 32, 0, st>>>(c->params, idx, out, n, n_dev);
+        coala_gather_kernel<VPL, SYS><<<1, 32, 0, st>>>(c->params, idx, out, n, n_dev, next_work(c));
     } else {
-        // A fixed grid of `waves` x (resident CTAs); every warp takes one contiguous chunk of the rows
-        // (sized on the device from the real count).  Two waves by default: CTAs retire early enough
-        // for the next batch's sampling kernels (higher-priority stream) to get SM slots, and long
-        // enough for a warp to pipeline several rows.  COALA_GATHER_WAVES overrides.
-        //
-        // SM budget: the gather is bandwidth bound and saturates its link with 16 warps per SM, while the
-        // next batch's sampling kernels (other stream) are latency bound and need resident warps to keep
-        // host round trips in flight.  `ctas_per_sm` caps the gather's residency by reserving (unused)
-        // dynamic shared memory, so registers and warp slots stay free for the sampler instead of the
-        // two kernels taking turns.  COALA_GATHER_CTAS_PER_SM overrides (0 = no cap).
         const int threads = 256, wpb = threads / 32;
-        int resident = MINB;
-        size_t smem = 0;
-        if (c->ctas_per_sm > 0 && c->ctas_per_sm < MINB) {
-            resident = c->ctas_per_sm;
-            // big enough that resident+1 CTAs cannot fit, small enough to leave >= 16 KB per SM for the
-            // (1 KB each) driver reservations of the other stream's CTAs
-            smem = (size_t)(c->smem_per_sm / resident) - 16384;
-            // per device, and cheap: set on every launch rather than tracking (device, instantiation) pairs
-            COALA_CUDA(cudaFuncSetAttribute(coala_gather_kernel<VPL, SYS, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        }
-        int64_t blocks = (int64_t)c->sm_count * resident * c->waves;
-        const int64_t need = (n + wpb - 1) / wpb;
+        const int resident = c->ctas_per_sm;
+        // big enough that resident+1 CTAs cannot fit, small enough to leave >= 16 KB per SM for the
+        // (1 KB each) driver reservations of the other streams' CTAs
+        const size_t smem = (size_t)(c->smem_per_sm / resident) - 16384;
+        // per device, and cheap: set on every launch rather than tracking (device, instantiation) pairs
+        COALA_CUDA(cudaFuncSetAttribute(coala_gather_kernel<VPL, SYS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        int64_t blocks = (int64_t)c->sm_count * resident;
+        const int64_t need = (n + (int64_t)wpb * GATHER_CH - 1) / ((int64_t)wpb * GATHER_CH);
         if (blocks > need) blocks = need;
-        coala_gather_kernel<VPL, SYS, MINB><<<(unsigned)blocks, threads, smem, st>>>(c->params, idx, out, n, n_dev);
+        coala_gather_kernel<VPL, SYS><<<(unsigned)blocks, threads, smem, st>>>(c->params, idx, out, n, n_dev, next_work(c));
     }
     COALA_CUDA(cudaGetLastError());
     return 0;
 }
 
-// Copy engine 1 (bulk asynchronous copies through shared memory, see cache.cuh).  Two row buffers per warp;
+// Copy engine 1 (bulk asynchronous copies through shared memory, see cache.cuh).  NBUF row buffers per warp;
 // the dynamic shared memory doubles as the residency cap (2 CTAs per SM).
 template <int VPL, bool SYS, int NBUF>
 static int launch_gather_bulk(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st) {
@@ -125,10 +122,10 @@ static int launch_gather_bulk(coala_cache* c, const int64_t* idx, float* out, in
     size_t smem = (size_t)(c->smem_per_sm / resident) - 16384;
     if (smem < need_smem) smem = need_smem;
     COALA_CUDA(cudaFuncSetAttribute(coala_gather_bulk_kernel<VPL, SYS, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int64_t blocks = (int64_t)c->sm_count * resident * c->bulk_waves;
-    const int64_t need = (n + wpb - 1) / wpb;
+    int64_t blocks = (int64_t)c->sm_count * resident;
+    const int64_t need = (n + (int64_t)wpb * GATHER_CH - 1) / ((int64_t)wpb * GATHER_CH);
     if (blocks > need) blocks = need;
-    coala_gather_bulk_kernel<VPL, SYS, NBUF><<<(unsigned)blocks, threads, smem, st>>>(c->params, idx, out, n, n_dev);
+    coala_gather_bulk_kernel<VPL, SYS, NBUF><<<(unsigned)blocks, threads, smem, st>>>(c->params, idx, out, n, n_dev, next_work(c));
     COALA_CUDA(cudaGetLastError());
     return 0;
 }
@@ -153,12 +150,8 @@ static int dispatch_gather(coala_cache* c, const int64_t* idx, float* out, int64
         }
 #undef COALA_GOB
     }
-#define COALA_GO(V)                                                                                    \
-    if (c->min_blocks == 2)                                                                            \
-        return sys ? launch_gather<V, true, 2>(c, idx, out, n, n_dev, st, serial)                      \
-                   : launch_gather<V, false, 2>(c, idx, out, n, n_dev, st, serial);                    \
-    return sys ? launch_gather<V, true, 3>(c, idx, out, n, n_dev, st, serial)                          \
-               : launch_gather<V, false, 3>(c, idx, out, n, n_dev, st, serial)
+#define COALA_GO(V) \
+    return sys ? launch_gather<V, true>(c, idx, out, n, n_dev, st, serial) : launch_gather<V, false>(c, idx, out, n, n_dev, st, serial)
     switch (vpl) {
         case 1: COALA_GO(1);
         case 2: COALA_GO(2);
@@ -220,6 +213,8 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     COALA_CUDA_NULL(cudaMemcpy(c->slab, &hdr, sizeof(hdr), cudaMemcpyHostToDevice));
     COALA_CUDA_NULL(cudaMalloc(&c->d_stats, 4 * sizeof(unsigned long long)));
     COALA_CUDA_NULL(cudaMemset(c->d_stats, 0, 4 * sizeof(unsigned long long)));
+    COALA_CUDA_NULL(cudaMalloc(&c->d_work, GATHER_WORK_POOL * sizeof(GatherWork)));
+    COALA_CUDA_NULL(cudaMemset(c->d_work, 0, GATHER_WORK_POOL * sizeof(GatherWork)));
 
     CacheParams& p = c->params;
     memset(&p, 0, sizeof(p));
@@ -241,12 +236,9 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     p.id_limit = TAG_ID_MASK;
     if (nd && coala_nd_num_graph_nodes(nd) > 0 && (uint64_t)coala_nd_num_graph_nodes(nd) < p.id_limit)
         p.id_limit = (uint64_t)coala_nd_num_graph_nodes(nd);
-    if (const char* e = getenv("COALA_GATHER_MINB")) c->min_blocks = atoi(e) == 2 ? 2 : 3;
-    if (const char* e = getenv("COALA_GATHER_CTAS_PER_SM")) c->ctas_per_sm = atoi(e);
+    if (const char* e = getenv("COALA_GATHER_CTAS_PER_SM")) c->ctas_per_sm = atoi(e) >= 1 && atoi(e) <= 3 ? atoi(e) : 2;
     if (const char* e = getenv("COALA_GATHER_ENGINE")) c->copy_engine = atoi(e) == 1 ? 1 : 0;
     if (const char* e = getenv("COALA_GATHER_NBUF")) c->bulk_nbuf = atoi(e) == 2 ? 2 : 3;
-    if (const char* e = getenv("COALA_GATHER_BULK_WAVES")) c->bulk_waves = atoi(e) > 0 ? atoi(e) : 2;
-    if (const char* e = getenv("COALA_GATHER_WAVES")) c->waves = atoi(e) > 0 ? atoi(e) : 2;
 
     cudaDeviceProp prop;
     COALA_CUDA_NULL(cudaGetDeviceProperties(&prop, device));
@@ -267,6 +259,7 @@ extern "C" void coala_cache_destroy(coala_cache* c) {
     if (c->vmm) vmm_free(&c->region);
     else if (c->slab) cudaFree(c->slab);
     if (c->d_stats) cudaFree(c->d_stats);
+    if (c->d_work) cudaFree(c->d_work);
     delete c;
 }
 

@@ -229,68 +229,171 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
     return 1;
 }
 
+// Out-of-line copy of resolve_row for the bulk engine, where it is the rare path (misses, busy lines, failed validations):
+// keeps the register file of the bulk kernel's main loop for the pipeline state.
+template <int VPL, bool SYS>
+__device__ __noinline__ int resolve_row_call(const CacheParams& p, uint64_t id, int g, uint64_t set, uint64_t t, float* out_row, unsigned lane) {
+    return resolve_row<VPL, SYS>(p, id, g, set, t, out_row, lane);
+}
+
 // An id outside the host table (or wider than the tag's 40-bit id field) must not be dereferenced: its output
 // row is zero-filled and the launch counts it in stats[3]; the synchronous entry points turn that into an error.
 __device__ __forceinline__ void refuse_row(const CacheParams& p, float* out_row, unsigned lane) {
     for (int e = (int)lane; e < p.out_dim; e += 32) out_row[e] = 0.0f;
 }
 
-// Work split: the rows are cut into one contiguous chunk per warp from the DEVICE-side row count,
-// so the same launch shape serves any n (the count comes from the sampler and never visits the
-// host).  Within a chunk lane l owns row l's id and does the 64-bit owner/set arithmetic for it
-// once; ids, owners and sets are then broadcast by shuffle, and the tag probe of row i+1 is issued
-// before row i is copied, so a warp's rows overlap instead of paying idx -> tag -> row -> re-check
-// latencies back to back.
-template <int VPL, bool SYS, int MINB>
-__global__ void __launch_bounds__(256, MINB) coala_gather_kernel(CacheParams p, const int64_t* __restrict__ idx,
-                                                           float* __restrict__ out, int64_t n,
-                                                           const int64_t* __restrict__ n_dev) {
+// Work split: DYNAMIC.  One resident wave of CTAs; a warp takes chunks of GATHER_CH rows from a device-side counter until the
+// list is exhausted (the row count comes from the sampler and never visits the host).  A static cut (the first version of
+// this kernel: one contiguous run of rows per warp, two waves of CTAs) makes the launch as slow as its unluckiest warp: a row
+// served from local HBM, a peer's HBM over NVLink, or the host (+ the fill protocol) costs about 1 : 3 : 10, so with a mix the
+// per-link times ADDED UP instead of overlapping (2 GPUs, half the rows remote: 106 us against 53 us all-local and 170 us
+// all-remote; 3 % misses: +60 us = the host link's whole transfer time).  With a shared queue every warp is busy until the
+// list is empty, whatever its rows cost.
+//
+// The front end runs three chunks deep so that no row waits for it: while the rows of chunk k are copied, the tag probes of
+// chunk k+1 (GATHER_CH coalesced 256-B loads per warp, possibly over NVLink), the id loads of chunk k+2 and the counter
+// atomic of chunk k+3 are in flight.  Lane l < GATHER_CH owns row l of a chunk and does its 64-bit owner/set arithmetic
+// once; ids, owners and sets reach the other lanes by shuffle.  A tag probed one chunk early can be stale by the time it
+// is used; it is only a hint (the seqlock re-check / the probe under the set lock decide).
+constexpr int GATHER_CH = 4;
+// Register cap of both gather kernels: 2 resident CTAs x 256 threads x 96 = 48 K of the SM's 64 K registers, which leaves a
+// sampling CTA of another stream (256 threads x 54) room to be co-resident (ptxas: 16 bytes of spill at R = 4 KB, none below).
+#define GATHER_MAX_REGS 96
+
+struct GatherWork {       // one per in-flight launch (a small rotating pool per cache object)
+    unsigned next;        // next chunk block to hand out
+    unsigned done;        // CTAs that have finished (the last one re-arms both words for a later launch)
+};
+
+template <bool SYS>
+struct RowFeeder {
+    const CacheParams& p;
+    const int64_t* idx;
+    int64_t n;
+    GatherWork* wk;
+    unsigned lane, n_chunks, per_grab;
+    unsigned blk_next = 0, blk_left = 0;
+    bool dry = false;
+    unsigned cA, cB, cC;                 // chunk being copied, chunk being probed, chunk whose ids are loading
+    uint64_t idA = 0, idB = 0, idC = 0;
+    int gA = 0, gB = 0, gC = 0;
+    uint32_t setA = 0, setB = 0, setC = 0;
+    uint64_t tA[GATHER_CH], tB[GATHER_CH];
+
+    __device__ __forceinline__ RowFeeder(const CacheParams& p_, const int64_t* idx_, int64_t n_, GatherWork* wk_, unsigned lane_)
+        : p(p_), idx(idx_), n(n_), wk(wk_), lane(lane_) {
+        n_chunks = (unsigned)((n + GATHER_CH - 1) / GATHER_CH);
+        // one counter atomic hands out ~16 KB of rows: 1 chunk of 4 KB rows, 8 chunks of 512-B rows
+        per_grab = 4096u / p.row_bytes;
+        if (per_grab < 1) per_grab = 1;
+    }
+    __device__ __forceinline__ unsigned grab() {
+        if (blk_left == 0) {
+            if (dry) return n_chunks;
+            unsigned base = 0;
+            if (lane == 0) base = atomicAdd(&wk->next, per_grab);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            if (base >= n_chunks) { dry = true; return n_chunks; }
+            blk_next = base;
+            blk_left = per_grab;
+        }
+        blk_left--;
+        const unsigned c = blk_next++;
+        return c < n_chunks ? c : n_chunks;
+    }
+    __device__ __forceinline__ void load_ids(unsigned c, uint64_t& id, int& g, uint32_t& set) const {
+        id = 0; g = p.my_slot; set = 0;
+        const int64_t row = (int64_t)c * GATHER_CH + lane;
+        if (c < n_chunks && lane < GATHER_CH && row < n) {
+            id = (uint64_t)__ldg(idx + row);
+            if (p.route_gpus > 1) g = (int)(id % (uint64_t)p.route_gpus);
+            set = (uint32_t)((id / (uint64_t)p.hash_div) % p.num_sets);
+        }
+    }
+    __device__ __forceinline__ void probe(unsigned c, uint64_t id, int g, uint32_t set, uint64_t (&t)[GATHER_CH]) const {
+#pragma unroll
+        for (int i = 0; i < GATHER_CH; i++) {
+            const int gi = __shfl_sync(0xffffffffu, g, i);
+            const uint32_t si = __shfl_sync(0xffffffffu, set, i);
+            t[i] = 0;
+            if (c < n_chunks && (int64_t)c * GATHER_CH + i < n)
+                t[i] = ld_relaxed_u64<SYS>(p.shard[gi].tags + (uint64_t)si * COALA_WAYS + lane);
+        }
+    }
+    __device__ __forceinline__ void start() {
+        cA = grab(); cB = grab(); cC = grab();
+        load_ids(cA, idA, gA, setA);
+        load_ids(cB, idB, gB, setB);
+        probe(cA, idA, gA, setA, tA);
+    }
+    __device__ __forceinline__ bool have() const { return cA < n_chunks; }
+    // issue the loads of the stages behind chunk A (call before copying A's rows)
+    __device__ __forceinline__ unsigned prefetch() {
+        probe(cB, idB, gB, setB, tB);
+        load_ids(cC, idC, gC, setC);
+        return grab();
+    }
+    __device__ __forceinline__ void rotate(unsigned cD) {
+        cA = cB; idA = idB; gA = gB; setA = setB;
+#pragma unroll
+        for (int i = 0; i < GATHER_CH; i++) tA[i] = tB[i];
+        cB = cC; idB = idC; gB = gC; setB = setC;
+        cC = cD;
+    }
+    __device__ __forceinline__ int rows_in_A() const {
+        const int64_t left = n - (int64_t)cA * GATHER_CH;
+        return left < GATHER_CH ? (int)left : GATHER_CH;
+    }
+};
+
+// the last CTA out re-arms the work counter for a later launch that gets the same pool entry
+__device__ __forceinline__ void gather_work_done(GatherWork* wk) {
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        __threadfence();
+        if (atomicAdd(&wk->done, 1u) == gridDim.x - 1) {
+            wk->next = 0;
+            wk->done = 0;
+            __threadfence();
+        }
+    }
+}
+
+template <int VPL, bool SYS>
+__global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_kernel(const __grid_constant__ CacheParams p, const int64_t* __restrict__ idx,
+                                                              float* __restrict__ out, int64_t n,
+                                                              const int64_t* __restrict__ n_dev, GatherWork* wk) {
     __shared__ unsigned s_stat[3];
     if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
     __syncthreads();
     if (n_dev) n = min(n, *n_dev);
     const unsigned lane = lane_id();
-    const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
-    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int64_t rpw = (n + warps_total - 1) / warps_total;
-    const int64_t end = min(n, (w + 1) * rpw);
     unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
-    for (int64_t base = w * rpw; base < end; base += 32) {
-        const int cnt = (int)min((int64_t)32, end - base);
-        uint64_t my_id = 0;
-        int my_g = p.my_slot;
-        uint32_t my_set = 0;
-        if ((int)lane < cnt) {
-            my_id = (uint64_t)__ldg(idx + base + lane);
-            if (p.route_gpus > 1) my_g = (int)(my_id % (uint64_t)p.route_gpus);
-            my_set = (uint32_t)((my_id / (uint64_t)p.hash_div) % p.num_sets);
-        }
-        uint64_t id = __shfl_sync(0xffffffffu, my_id, 0);
-        int g = __shfl_sync(0xffffffffu, my_g, 0);
-        uint32_t set = __shfl_sync(0xffffffffu, my_set, 0);
-        uint64_t t = ld_relaxed_u64<SYS>(p.shard[g].tags + (uint64_t)set * COALA_WAYS + lane);
-        for (int i = 0; i < cnt; i++) {
-            uint64_t id_n = 0, t_n = 0;
-            int g_n = 0;
-            uint32_t set_n = 0;
-            if (i + 1 < cnt) {
-                id_n = __shfl_sync(0xffffffffu, my_id, i + 1);
-                g_n = __shfl_sync(0xffffffffu, my_g, i + 1);
-                set_n = __shfl_sync(0xffffffffu, my_set, i + 1);
-                t_n = ld_relaxed_u64<SYS>(p.shard[g_n].tags + (uint64_t)set_n * COALA_WAYS + lane);
+    RowFeeder<SYS> f(p, idx, n, wk, lane);
+    f.start();
+    while (f.have()) {
+        const unsigned cD = f.prefetch();
+        const int cnt = f.rows_in_A();
+        const int64_t base = (int64_t)f.cA * GATHER_CH;
+#pragma unroll
+        for (int i = 0; i < GATHER_CH; i++) {
+            if (i < cnt) {
+                const uint64_t id = __shfl_sync(0xffffffffu, f.idA, i);
+                const int g = __shfl_sync(0xffffffffu, f.gA, i);
+                const uint32_t set = __shfl_sync(0xffffffffu, f.setA, i);
+                float* out_row = out + (base + i) * (int64_t)p.out_stride;
+                if (id < p.id_limit) {
+                    const int res = resolve_row<VPL, SYS>(p, id, g, set, f.tA[i], out_row, lane);
+                    n_hit += res == 0;
+                    n_miss += res == 1;
+                    n_byp += res == 2;
+                } else {
+                    refuse_row(p, out_row, lane);
+                    n_bad++;
+                }
             }
-            float* out_row = out + (base + i) * (int64_t)p.out_stride;
-            if (id < p.id_limit) {
-                const int res = resolve_row<VPL, SYS>(p, id, g, set, t, out_row, lane);
-                n_hit += res == 0;
-                n_miss += res == 1;
-                n_byp += res == 2;
-            } else {
-                refuse_row(p, out_row, lane);
-                n_bad++;
-            }
-            id = id_n; g = g_n; set = set_n; t = t_n;
         }
+        f.rotate(cD);
     }
     if (lane == 0) {
         if (n_hit) atomicAdd(&s_stat[0], n_hit);
@@ -300,6 +403,7 @@ __global__ void __launch_bounds__(256, MINB) coala_gather_kernel(CacheParams p, 
     }
     __syncthreads();
     if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
+    gather_work_done(wk);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -347,9 +451,9 @@ struct BulkPending {   // a hit row whose line is on its way into shared memory
 };
 
 template <int VPL, bool SYS, int NBUF>
-__global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p, const int64_t* __restrict__ idx,
+__global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_bulk_kernel(const __grid_constant__ CacheParams p, const int64_t* __restrict__ idx,
                                                                    float* __restrict__ out, int64_t n,
-                                                                   const int64_t* __restrict__ n_dev) {
+                                                                   const int64_t* __restrict__ n_dev, GatherWork* wk) {
     static_assert(NBUF == 2 || NBUF == 3, "queue below is written for one or two waiting rows");
     extern __shared__ __align__(128) uint8_t dyn_smem[];
     __shared__ uint64_t bars[8][NBUF];
@@ -365,10 +469,6 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
     }
     __syncthreads();
     if (n_dev) n = min(n, *n_dev);
-    const int64_t warps_total = (int64_t)gridDim.x * (blockDim.x >> 5);
-    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + wib;
-    const int64_t rpw = (n + warps_total - 1) / warps_total;
-    const int64_t end = min(n, (w + 1) * rpw);
     const uint32_t out_bytes = (uint32_t)p.out_dim * 4;
     unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
     unsigned phase_bits = 0;   // bit b = parity the next wait on buffer b expects
@@ -391,36 +491,25 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
             count(0);
         } else {  // the line changed under the copy: redo the row through the register path
             const uint64_t t = ld_relaxed_u64<SYS>(sh.tags + (uint64_t)q0.set * COALA_WAYS + lane);
-            count(resolve_row<VPL, SYS>(p, q0.id, g, q0.set, t, out_row, lane));
+            count(resolve_row_call<VPL, SYS>(p, q0.id, g, q0.set, t, out_row, lane));
         }
         q0 = q1;
         waiting--;
     };
 
-    for (int64_t base = w * rpw; base < end; base += 32) {
-        const int cnt = (int)min((int64_t)32, end - base);
-        uint64_t my_id = 0;
-        int my_g = p.my_slot;
-        uint32_t my_set = 0;
-        if ((int)lane < cnt) {
-            my_id = (uint64_t)__ldg(idx + base + lane);
-            if (p.route_gpus > 1) my_g = (int)(my_id % (uint64_t)p.route_gpus);
-            my_set = (uint32_t)((my_id / (uint64_t)p.hash_div) % p.num_sets);
-        }
-        uint64_t id = __shfl_sync(0xffffffffu, my_id, 0);
-        int g = __shfl_sync(0xffffffffu, my_g, 0);
-        uint32_t set = __shfl_sync(0xffffffffu, my_set, 0);
-        uint64_t t = ld_relaxed_u64<SYS>(p.shard[g].tags + (uint64_t)set * COALA_WAYS + lane);
-        for (int i = 0; i < cnt; i++) {
-            uint64_t id_n = 0, t_n = 0;
-            int g_n = 0;
-            uint32_t set_n = 0;
-            if (i + 1 < cnt) {
-                id_n = __shfl_sync(0xffffffffu, my_id, i + 1);
-                g_n = __shfl_sync(0xffffffffu, my_g, i + 1);
-                set_n = __shfl_sync(0xffffffffu, my_set, i + 1);
-                t_n = ld_relaxed_u64<SYS>(p.shard[g_n].tags + (uint64_t)set_n * COALA_WAYS + lane);
-            }
+    RowFeeder<SYS> f(p, idx, n, wk, lane);
+    f.start();
+    while (f.have()) {
+        const unsigned cD = f.prefetch();
+        const int cnt = f.rows_in_A();
+        const int64_t base = (int64_t)f.cA * GATHER_CH;
+#pragma unroll
+        for (int i = 0; i < GATHER_CH; i++) {
+            if (i >= cnt) continue;
+            const uint64_t id = __shfl_sync(0xffffffffu, f.idA, i);
+            const int g = __shfl_sync(0xffffffffu, f.gA, i);
+            const uint32_t set = __shfl_sync(0xffffffffu, f.setA, i);
+            const uint64_t t = f.tA[i];
             const unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
             const unsigned way = m ? __ffs(m) - 1 : 0;
             const uint64_t tw = __shfl_sync(0xffffffffu, t, way);
@@ -443,10 +532,10 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
                 waiting++;
                 cur = cur + 1 == NBUF ? 0 : cur + 1;
             } else {
-                count(resolve_row<VPL, SYS>(p, id, g, set, t, out + (base + i) * (int64_t)p.out_stride, lane));
+                count(resolve_row_call<VPL, SYS>(p, id, g, set, t, out + (base + i) * (int64_t)p.out_stride, lane));
             }
-            id = id_n; g = g_n; set = set_n; t = t_n;
         }
+        f.rotate(cD);
     }
     while (waiting) complete_oldest();
     if (lane == 0) {
@@ -458,4 +547,5 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(CacheParams p
     }
     __syncthreads();
     if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
+    gather_work_done(wk);
 }

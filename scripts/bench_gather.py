@@ -200,16 +200,17 @@ if args.gpus >= 2:
     timed("p2p_local_only_warm", [(D0, caches[0])], [even], iters=len(even))
     timed("p2p_local_only_one", [(D0, caches[0])], [even], iters=args.iters)
     timed("p2p_remote_only_both", [(D0, caches[0]), (D1, caches[1])], [odd, even], iters=args.iters)
-    # peer-link streaming-read probe: GPU 0 reads GPU 1's memory
+    # peer-link streaming-read probe: GPU 0 reads GPU 1's memory (a plain cudaMalloc buffer needs classic peer access)
     torch.cuda.set_device(1)
     peer_buf = torch.empty(1 << 30, dtype=torch.uint8, device="cuda:1")
     torch.cuda.set_device(0)
-    # the shards are VMM mappings; this plain buffer needs classic peer access, which torch enables on the
-    # first cross-device copy
-    peer_buf[:4096].to("cuda:0")
-    torch.cuda.synchronize()
-    check(L.coala_probe_read_bandwidth(peer_buf.data_ptr(), 1 << 30, 5, C.byref(gb)))
-    res["nvlink_read_GBs"] = gb.value
+    rc = torch.cuda.cudart().cudaDeviceEnablePeerAccess(1, 0)
+    if int(rc) in (0, 704):  # success | already enabled
+        torch.cuda.synchronize()
+        check(L.coala_probe_read_bandwidth(peer_buf.data_ptr(), 1 << 30, 5, C.byref(gb)))
+        res["nvlink_read_GBs"] = gb.value
+    else:
+        res["nvlink_read_GBs"] = "peer access unavailable (cudaDeviceEnablePeerAccess rc %s)" % rc
 torch.cuda.set_device(0)
 devbuf = torch.empty(1 << 30, dtype=torch.uint8, device="cuda:0")
 check(L.coala_probe_read_bandwidth(devbuf.data_ptr(), 1 << 30, 5, C.byref(gb)))

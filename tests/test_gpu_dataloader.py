@@ -128,4 +128,5 @@ def test_device_pipeline_two_stream_prefetch_is_bit_exact(tmp_path, backend, pre
         assert np.array_equal(blocks[0].edge_id.cpu().numpy(), eblocks[0]["edge_id"])
         rows = out[:len(einp)].cpu().numpy()
         assert np.array_equal(rows.view(np.uint32), d["feat"][einp].view(np.uint32))
-    assert len(pipe.gather_ms()) >= n_steps - 2
+    g_ms = pipe.gather_ms()  # [mean CUDA-event time of the gather launches] from the native engine
+    assert len(g_ms) == 1 and 0.0 < g_ms[0] < 50.0
