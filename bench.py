@@ -58,7 +58,7 @@ def parse_args():
     p.add_argument("--cpu_baseline_seconds", type=float, default=12.0)
     p.add_argument("--no_cpu_baseline", action="store_true")
     p.add_argument("--extras", default=os.environ.get("COALA_BENCH_EXTRAS", "auto"),
-                   help="auto | none | comma list of all_resident,distribution,backends")
+                   help="auto | none | comma list of all_resident,distribution,backends,stress")
     p.add_argument("--extras_budget", type=float, default=300.0, help="seconds after which the extras are abandoned and the main line printed")
     p.add_argument("--hbm_indptr", action="store_true", help="B200 option: sampler keeps a copy of indptr (80 MB) in HBM")
     p.add_argument("--no_prefetch", action="store_true", help="diagnostic: sample and gather of a batch back to back, no batch in flight")
@@ -738,19 +738,27 @@ def extra_backends(args, st):
     return out
 
 
+def extra_stress(args, st):
+    """Cross-GPU eviction storm (tests/multi_gpu_stress.py): every rank hammers the same two sets of every shard of a 1 MB
+    partitioned cache at once, launches alternating between the copy engines, every row of every launch checked bitwise."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from multi_gpu_stress import eviction_storm
+    return eviction_storm(st["comm"], st["device"], 3000, tag="%s_storm" % os.environ.get("MASTER_PORT", str(os.getpid())))
+
+
 def run_extras(args, st, out):
     comm = st["comm"]
     N = comm.global_size
     want = args.extras
     if want == "none":
         return
-    names = ["all_resident"] + (["distribution", "backends"] if N >= 2 else [])
+    names = ["all_resident"] + (["distribution", "backends", "stress"] if N >= 2 else [])
     if want != "auto":
-        names = [n for n in want.split(",") if n in ("all_resident", "distribution", "backends") and (N >= 2 or n == "all_resident")]
+        names = [n for n in want.split(",") if n in ("all_resident", "distribution", "backends", "stress") and (N >= 2 or n == "all_resident")]
     if comm.num_master_process != 1:
         names = [n for n in names if n == "all_resident"]
     extras = {}
-    fns = {"all_resident": extra_all_resident, "distribution": extra_distribution, "backends": extra_backends}
+    fns = {"all_resident": extra_all_resident, "distribution": extra_distribution, "backends": extra_backends, "stress": extra_stress}
     for n in names:
         t0 = time.time()
         extras[n] = fns[n](args, st)

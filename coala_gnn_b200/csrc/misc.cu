@@ -176,6 +176,81 @@ extern "C" int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int i
 }
 
 // ------------------------------------------------------------------------------------------
+// row-gather probe: out[i] = table[idx[i]] for rows of `row_bytes`, NO cache protocol (no tags, no validation) - the
+// practical ceiling of the gather's access pattern on a link (local HBM, a peer's HBM, pinned host), against which the
+// cache kernel's protocol overhead is read.  One warp per row, RIF rows in flight per warp, 16-byte vectors.
+// ------------------------------------------------------------------------------------------
+template <int VPL, int RIF>
+__global__ void probe_gather_kernel(const uint4* __restrict__ table, const int64_t* __restrict__ idx, uint4* __restrict__ out, int64_t n) {
+    const unsigned lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    constexpr int RV = VPL * 32;  // 16-byte vectors per row
+    for (int64_t r = w * RIF; r < n; r += warps * RIF) {
+        uint4 v[RIF][VPL];
+#pragma unroll
+        for (int j = 0; j < RIF; j++) {
+            if (r + j < n) {
+                const uint4* src = table + (uint64_t)__ldg(idx + r + j) * RV;
+#pragma unroll
+                for (int k = 0; k < VPL; k++) v[j][k] = ld_host_v4(src + k * 32 + lane);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < RIF; j++) {
+            if (r + j < n) {
+                uint4* dst = out + (uint64_t)(r + j) * RV;
+#pragma unroll
+                for (int k = 0; k < VPL; k++) st_out_v4(dst + k * 32 + lane, v[j][k]);
+            }
+        }
+    }
+}
+
+// Times `iters` launches (each over its own n ids: idx holds iters * n of them, so no launch re-reads rows that an earlier
+// one left in L2) with CUDA events; us_per_launch = mean.  rows_in_flight 1|2, ctas_per_sm 1..8 CTAs of 256 threads.
+extern "C" int coala_probe_gather(uint64_t table_ptr, uint64_t idx_ptr, uint64_t out_ptr, int64_t n, int row_bytes, int rows_in_flight,
+                                  int ctas_per_sm, int iters, double* us_per_launch) {
+    if (row_bytes != 512 && row_bytes != 1024 && row_bytes != 2048 && row_bytes != 4096) COALA_FAIL("probe_gather: row_bytes 512..4096");
+    if (rows_in_flight != 1 && rows_in_flight != 2) COALA_FAIL("probe_gather: rows_in_flight 1 or 2");
+    int dev = 0, sms = 148;
+    COALA_CUDA(cudaGetDevice(&dev));
+    COALA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    const unsigned grid = (unsigned)(sms * (ctas_per_sm < 1 ? 1 : ctas_per_sm));
+    const uint4* t = reinterpret_cast<const uint4*>(table_ptr);
+    const int64_t* ix = reinterpret_cast<const int64_t*>(idx_ptr);
+    uint4* o = reinterpret_cast<uint4*>(out_ptr);
+    cudaEvent_t e0, e1;
+    COALA_CUDA(cudaEventCreate(&e0));
+    COALA_CUDA(cudaEventCreate(&e1));
+    auto go = [&](int it) {
+        const int64_t* p = ix + (int64_t)it * n;
+#define COALA_PG(V)                                                                 \
+    if (rows_in_flight == 2) probe_gather_kernel<V, 2><<<grid, 256>>>(t, p, o, n);  \
+    else probe_gather_kernel<V, 1><<<grid, 256>>>(t, p, o, n)
+        switch (row_bytes / 512) {
+            case 1: COALA_PG(1); break;
+            case 2: COALA_PG(2); break;
+            case 4: COALA_PG(4); break;
+            default: COALA_PG(8); break;
+        }
+#undef COALA_PG
+    };
+    go(0);  // warm-up (its rows are not reused: timed launches start at it = 1 when there are several)
+    COALA_CUDA(cudaDeviceSynchronize());
+    COALA_CUDA(cudaEventRecord(e0));
+    for (int i = 0; i < iters; i++) go(iters > 1 ? i : 0);
+    COALA_CUDA(cudaEventRecord(e1));
+    COALA_CUDA(cudaEventSynchronize(e1));
+    COALA_CUDA(cudaGetLastError());
+    float ms = 0;
+    COALA_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    *us_per_launch = 1e3 * ms / iters;
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------
 // random small-read probe: how many independent locations per second a link serves when every
 // location is read as `span` contiguous bytes (8, 32, 64, 128 or 256) by neighbouring lanes.  Tells whether
 // the link charges per request or per 32-byte sector — the design input of the UVA sampler.

@@ -285,6 +285,12 @@ int coala_synth_check_rows(uint64_t rows_ptr, uint64_t idx_ptr, int64_t n, int d
 /* streaming-read bandwidth probe of a device-visible range (host link / peer link / HBM peaks) */
 int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int iters, double* gb_per_s);
 
+/* row-gather probe: out[i] = table[idx[i]] with no cache protocol - the practical ceiling of the gather's access pattern on
+ * whatever link `table` sits behind (local HBM, a peer's HBM, pinned host).  idx holds iters * n ids (one list per timed
+ * launch); rows_in_flight 1|2 per warp; ctas_per_sm CTAs of 256 threads per SM; returns the mean launch time (CUDA events). */
+int coala_probe_gather(uint64_t table_ptr, uint64_t idx_ptr, uint64_t out_ptr, int64_t n, int row_bytes, int rows_in_flight,
+                       int ctas_per_sm, int iters, double* us_per_launch);
+
 /* random-read probe: independent locations per second when each location is read as `span_bytes`
  * (8/32/64/128/256) contiguous bytes by neighbouring lanes; misalign != 0 starts 96 B into a 256-B granule */
 int coala_probe_random_read(uint64_t src_ptr, int64_t bytes, int span_bytes, int misalign, int warps, int iters,

@@ -30,6 +30,7 @@ ap.add_argument("--dim", type=int, default=1024)
 ap.add_argument("--gpus", type=int, default=1)
 ap.add_argument("--rows", type=int, default=25000)
 ap.add_argument("--iters", type=int, default=6)
+ap.add_argument("--regimes", default="", help="comma list of labels to time (default all); the warm-up launches they need still run")
 args = ap.parse_args()
 N, DIM, R = args.nodes, args.dim, args.rows
 L = lib()
@@ -65,9 +66,24 @@ def verify(D, idx_t, n):
     assert bad.value == 0, "%d corrupt rows" % bad.value
 
 
+WANT = set(x for x in args.regimes.split(",") if x)
+# warm-up launches a timed regime depends on
+NEEDS = {"iso_cold": ("iso_hit", "iso_miss01", "iso_miss03", "iso_miss10"), "iso_seq_warm": ("iso_seq_hit",), "iso_clustered_warm": ("iso_clustered_hit",),
+         "part1_cold": ("part1_hit", "part1_miss01", "part1_miss03", "part1_miss10"),
+         "p2p_cold_one": ("p2p_hit_one", "p2p_hit_both", "p2p_miss01_both", "p2p_miss03_both", "p2p_miss10_both"),
+         "p2p_seq_warm": ("p2p_seq_hit_both",), "p2p_clustered_warm": ("p2p_clustered_hit_both", "p2p_clustered_hit_one"),
+         "p2p_remote_only_warm": ("p2p_remote_only_one", "p2p_remote_only_both"), "p2p_local_only_warm": ("p2p_local_only_one",)}
+
+
+def wanted(label):
+    return not WANT or label in WANT or any(x in WANT for x in NEEDS.get(label, ()))
+
+
 def timed(label, jobs, batches_per_job, iters=None):
     """jobs: list of (D, cache); batches_per_job: list (per job) of lists of id arrays. Launches all jobs
     back to back per iteration (they run concurrently on different GPUs)."""
+    if not wanted(label):
+        return
     iters = iters or len(batches_per_job[0])
     ts = [[] for _ in jobs]
     for it in range(iters):

@@ -26,70 +26,77 @@ from coala_gnn_b200._lib import lib, check  # noqa: E402
 from coala_gnn_b200.datasets import SyntheticSharedCSCUVA  # noqa: E402
 from coala_gnn_b200 import synth  # noqa: E402
 
-ap = argparse.ArgumentParser()
-ap.add_argument("--launches", type=int, default=10000)
-ap.add_argument("--rows", type=int, default=4096, help="ids per launch")
-ap.add_argument("--sets", type=int, default=2, help="sets of every shard the id pool falls into")
-ap.add_argument("--check_every", type=int, default=1)
-args = ap.parse_args()
 
-comm = MPI_Comm_Manager(-1)
-torch.cuda.set_device(comm.device_index)
-device = "cuda:%d" % comm.device_index
-G = comm.local_size
-ds = SyntheticSharedCSCUVA("tiny", comm, device, num_colors=64)
-train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=3))
-nd = Node_Distributor(comm, train, 256, ds.color_file, ds.topk_file, ds.score_file)
-loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, MultiLayerNeighborSampler([5, 5], seed=1, rank=comm.global_rank),
-                              256, ds.dim, [5, 5], 1, device, cache_backend="nvshmem", sim_buf=ds.feat_data)  # 1 MB shard: 64 sets x 32 ways
-cache = loader.COALA_GNN_Manager.COALA_GNN_Cache
-cache.set_num_nodes(ds.num_nodes)
-S = cache.num_sets()
-ids = np.arange(ds.num_nodes, dtype=np.int64)
-pool = ids[((ids // G) % S) < args.sets]  # partitioned hashing: owner id % G, set (id / G) % S (M/cache_kernel.cu:11, M/nvshmem_cache.h:193-196)
-assert len(pool) > 32 * args.sets * G * 2, "pool must overflow the sets it maps to"
-rng = np.random.default_rng(100 + comm.global_rank)
-n_lists = 64
-lists = [torch.from_numpy(pool[rng.integers(0, len(pool), args.rows)]).to(device) for _ in range(n_lists)]
-out = torch.empty((args.rows, ds.dim), dtype=torch.float32, device=device)
-st = torch.cuda.current_stream().cuda_stream
-bad = C.c_int64()
-total_bad, total = 0, 0
-comm.global_comm.Barrier()
-t0 = time.time()
-for it in range(args.launches):
-    idx = lists[(it * 7 + comm.global_rank) % n_lists]
-    cache.set_copy_engine(it & 1 if (it >> 3) & 1 else (it >> 1) & 1)  # both engines, in changing phase against the peers
-    cache.read_feature_async(out.data_ptr(), idx.data_ptr(), idx.numel(), 0, st)
-    total += idx.numel()
-    if it % args.check_every == 0:
-        check(lib().coala_synth_check_rows(out.data_ptr(), idx.data_ptr(), idx.numel(), ds.dim, ds.dim, ds.feat_seed, C.byref(bad)))
-        total_bad += int(bad.value)
-        if bad.value:
-            print("rank %d launch %d: %d corrupt rows" % (comm.global_rank, it, bad.value), flush=True)
-            break
-torch.cuda.synchronize()
-dt = time.time() - t0
-h, m, b = cache.stats()
-refused = cache.refused_ids()
-comm.global_comm.Barrier()  # every rank has stopped writing: the shards are quiescent now
-keys, cmeta, scnt = cache.export_state()
-res = keys != np.uint64(0xFFFFFFFFFFFFFFFF)
-line_ids = keys[res].astype(np.int64)
-dup = len(line_ids) - len(np.unique(line_ids))
-wrong_owner = int(np.count_nonzero(line_ids % G != comm.local_rank))
-t = torch.tensor([total_bad, total, h, m, b, refused, dup, wrong_owner], dtype=torch.int64, device=device)
-if comm.global_size > 1:
-    dist.all_reduce(t)
-tb, tot, hs, ms, bs, rf, dups, wo = [int(x) for x in t.tolist()]
-if comm.global_rank == 0:
-    print("stress %d ranks: %d launches x %d rows per rank in %.1f s, %d rows checked, corrupt %d, hit %d miss %d bypass %d, "
-          "refused %d, duplicate lines %d, lines in a wrong shard %d" % (comm.global_size, args.launches, args.rows, dt, tot, tb, hs, ms, bs, rf, dups, wo), flush=True)
-ok = tb == 0 and hs + ms + bs == tot and rf == 0 and dups == 0 and wo == 0 and ms > 0 and hs > 0
-del loader, cache
-torch.cuda.synchronize()
-comm.global_comm.Barrier()
-ds.cleanup()
-if comm.global_rank == 0:
-    print("multi_gpu_stress: all good" if ok else "multi_gpu_stress: FAILED", flush=True)
-sys.exit(0 if ok else 1)
+def eviction_storm(comm, device, launches, rows=4096, sets=2, check_every=1, tag=None):
+    """Runs the storm on the ranks of `comm` (one 1 x G domain) and returns the summed counters (same dict on every rank)."""
+    G = comm.local_size
+    ds = SyntheticSharedCSCUVA("tiny", comm, device, num_colors=64, tag=tag)
+    try:
+        train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=3))
+        nd = Node_Distributor(comm, train, 256, ds.color_file, ds.topk_file, ds.score_file)
+        loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, MultiLayerNeighborSampler([5, 5], seed=1, rank=comm.global_rank),
+                                      256, ds.dim, [5, 5], 1, device, cache_backend="nvshmem", sim_buf=ds.feat_data)  # 1 MB shard: 64 sets x 32 ways
+        cache = loader.COALA_GNN_Manager.COALA_GNN_Cache
+        cache.set_num_nodes(ds.num_nodes)
+        S = cache.num_sets()
+        ids = np.arange(ds.num_nodes, dtype=np.int64)
+        pool = ids[((ids // G) % S) < sets]  # partitioned hashing: owner id % G, set (id / G) % S (M/cache_kernel.cu:11, M/nvshmem_cache.h:193-196)
+        assert len(pool) > 32 * sets * G * 2, "pool must overflow the sets it maps to"
+        rng = np.random.default_rng(100 + comm.global_rank)
+        n_lists = 64
+        lists = [torch.from_numpy(pool[rng.integers(0, len(pool), rows)]).to(device) for _ in range(n_lists)]
+        out = torch.empty((rows, ds.dim), dtype=torch.float32, device=device)
+        st = torch.cuda.current_stream().cuda_stream
+        bad = C.c_int64()
+        total_bad, total = 0, 0
+        comm.global_comm.Barrier()
+        t0 = time.time()
+        for it in range(launches):
+            idx = lists[(it * 7 + comm.global_rank) % n_lists]
+            cache.set_copy_engine(it & 1 if (it >> 3) & 1 else (it >> 1) & 1)  # both engines, in changing phase against the peers
+            cache.read_feature_async(out.data_ptr(), idx.data_ptr(), idx.numel(), 0, st)
+            total += idx.numel()
+            if it % check_every == 0:
+                check(lib().coala_synth_check_rows(out.data_ptr(), idx.data_ptr(), idx.numel(), ds.dim, ds.dim, ds.feat_seed, C.byref(bad)))
+                total_bad += int(bad.value)
+                if bad.value:
+                    print("rank %d launch %d: %d corrupt rows" % (comm.global_rank, it, bad.value), flush=True)
+                    break
+        torch.cuda.synchronize()
+        dt = time.time() - t0
+        h, m, b = cache.stats()
+        refused = cache.refused_ids()
+        comm.global_comm.Barrier()  # every rank has stopped writing: the shards are quiescent now
+        keys, cmeta, scnt = cache.export_state()
+        res = keys != np.uint64(0xFFFFFFFFFFFFFFFF)
+        line_ids = keys[res].astype(np.int64)
+        dup = len(line_ids) - len(np.unique(line_ids))
+        wrong_owner = int(np.count_nonzero(line_ids % G != comm.local_rank))
+        t = torch.tensor([total_bad, total, h, m, b, refused, dup, wrong_owner], dtype=torch.int64, device=device)
+        if comm.global_size > 1:
+            dist.all_reduce(t)
+        tb, tot, hs, ms, bs, rf, dups, wo = [int(x) for x in t.tolist()]
+        ok = tb == 0 and hs + ms + bs == tot and rf == 0 and dups == 0 and wo == 0 and ms > 0 and hs > 0
+        del loader, cache, nd
+        torch.cuda.synchronize()
+        comm.global_comm.Barrier()
+        return {"ranks": comm.global_size, "launches_per_rank": launches, "rows_per_launch": rows, "seconds": round(dt, 2), "rows_checked": tot,
+                "corrupt_rows": tb, "hit": hs, "miss": ms, "bypass": bs, "refused": rf, "duplicate_lines": dups, "lines_in_wrong_shard": wo, "ok": ok}
+    finally:
+        ds.cleanup()
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--launches", type=int, default=10000)
+    ap.add_argument("--rows", type=int, default=4096, help="ids per launch")
+    ap.add_argument("--sets", type=int, default=2, help="sets of every shard the id pool falls into")
+    ap.add_argument("--check_every", type=int, default=1)
+    args = ap.parse_args()
+    comm = MPI_Comm_Manager(-1)
+    torch.cuda.set_device(comm.device_index)
+    r = eviction_storm(comm, "cuda:%d" % comm.device_index, args.launches, args.rows, args.sets, args.check_every)
+    if comm.global_rank == 0:
+        print("stress " + " ".join("%s=%s" % kv for kv in r.items()), flush=True)
+        print("multi_gpu_stress: all good" if r["ok"] else "multi_gpu_stress: FAILED", flush=True)
+    sys.exit(0 if r["ok"] else 1)
