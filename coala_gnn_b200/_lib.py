@@ -111,6 +111,7 @@ SIGNATURES = {
     "coala_synth_fill_features": (_i32, [_u64, _u64, _i64, _i64, _i32, _i64, _vp]),
     "coala_synth_check_rows": (_i32, [_u64, _u64, _i64, _i32, _i64, _u64, _vp]),
     "coala_probe_read_bandwidth": (_i32, [_u64, _i64, _i32, _vp]),
+    "coala_enable_peer_access": (_i32, [_i32, _i32]),
     "coala_probe_gather": (_i32, [_u64, _u64, _u64, _i64, _i32, _i32, _i32, _i32, _vp]),
     "coala_probe_random_read": (_i32, [_u64, _i64, _i32, _i32, _i32, _i32, _vp]),
 }

@@ -242,26 +242,25 @@ __device__ __forceinline__ void refuse_row(const CacheParams& p, float* out_row,
     for (int e = (int)lane; e < p.out_dim; e += 32) out_row[e] = 0.0f;
 }
 
-// Work split: DYNAMIC.  One resident wave of CTAs; a warp takes chunks of GATHER_CH rows from a device-side counter until the
-// list is exhausted (the row count comes from the sampler and never visits the host).  A static cut (the first version of
-// this kernel: one contiguous run of rows per warp, two waves of CTAs) makes the launch as slow as its unluckiest warp: a row
-// served from local HBM, a peer's HBM over NVLink, or the host (+ the fill protocol) costs about 1 : 3 : 10, so with a mix the
-// per-link times ADDED UP instead of overlapping (2 GPUs, half the rows remote: 106 us against 53 us all-local and 170 us
-// all-remote; 3 % misses: +60 us = the host link's whole transfer time).  With a shared queue every warp is busy until the
-// list is empty, whatever its rows cost.
+// Work split: DYNAMIC.  One resident wave of CTAs; a warp's first chunk of GATHER_CH rows is its own index, every further
+// one comes from a device-side counter until the list is exhausted (the row count comes from the sampler and never visits
+// the host).  A row served from local HBM, a peer's HBM over NVLink or the host (+ the fill protocol) costs about
+// 1 : 3 : 10 in warp time; a shared queue keeps every warp busy until the list is empty whatever its rows cost, and
+// because the wave is resident from the start the sampler's CTAs (other streams) never displace part of a gather.
 //
-// The front end runs three chunks deep so that no row waits for it: while the rows of chunk k are copied, the tag probes of
-// chunk k+1 (GATHER_CH coalesced 256-B loads per warp, possibly over NVLink), the id loads of chunk k+2 and the counter
-// atomic of chunk k+3 are in flight.  Lane l < GATHER_CH owns row l of a chunk and does its 64-bit owner/set arithmetic
-// once; ids, owners and sets reach the other lanes by shuffle.  A tag probed one chunk early can be stale by the time it
-// is used; it is only a hint (the seqlock re-check / the probe under the set lock decide).
+// Nothing in the steady state waits for the front end: the three dependent steps that open chunk k+1 - the counter
+// atomic, the id loads (lane l < GATHER_CH owns row l and does its 64-bit owner/set arithmetic once), the GATHER_CH
+// coalesced 256-B tag probes (possibly over NVLink) - are issued BETWEEN the rows of chunk k, one step per row, so each
+// has a row's copy time to complete and a warp never holds more than one unprocessed chunk (what it claims ahead is what
+// it cannot give back when the list runs dry).  A tag probed one chunk early can be stale by the time it is used; it is
+// only a hint (the seqlock re-check / the probe under the set lock decide).
 constexpr int GATHER_CH = 4;
-// Register cap of both gather kernels: 2 resident CTAs x 256 threads x 96 = 48 K of the SM's 64 K registers, which leaves a
-// sampling CTA of another stream (256 threads x 54) room to be co-resident (ptxas: 16 bytes of spill at R = 4 KB, none below).
+// Register cap of the register-path gather kernel: 2 resident CTAs x 256 threads x 96 = 48 K of the SM's 64 K registers,
+// which leaves a sampling CTA of another stream (256 threads x 54) room to be co-resident.
 #define GATHER_MAX_REGS 96
 
 struct GatherWork {       // one per in-flight launch (a small rotating pool per cache object)
-    unsigned next;        // next chunk block to hand out
+    unsigned next;        // next dynamic chunk block to hand out (chunk index - number of warps in the grid)
     unsigned done;        // CTAs that have finished (the last one re-arms both words for a later launch)
 };
 
@@ -271,13 +270,13 @@ struct RowFeeder {
     const int64_t* idx;
     int64_t n;
     GatherWork* wk;
-    unsigned lane, n_chunks, per_grab;
-    unsigned blk_next = 0, blk_left = 0;
-    bool dry = false;
-    unsigned cA, cB, cC;                 // chunk being copied, chunk being probed, chunk whose ids are loading
-    uint64_t idA = 0, idB = 0, idC = 0;
-    int gA = 0, gB = 0, gC = 0;
-    uint32_t setA = 0, setB = 0, setC = 0;
+    unsigned lane, n_chunks, per_grab, first_dyn;
+    unsigned blk_next = 0, blk_left = 0, raw = 0;
+    bool dry = false, claimed = false;
+    unsigned cA, cB;                     // chunk being copied, chunk being opened
+    uint64_t idA = 0, idB = 0;
+    int gA = 0, gB = 0;
+    uint32_t setA = 0, setB = 0;
     uint64_t tA[GATHER_CH], tB[GATHER_CH];
 
     __device__ __forceinline__ RowFeeder(const CacheParams& p_, const int64_t* idx_, int64_t n_, GatherWork* wk_, unsigned lane_)
@@ -286,20 +285,7 @@ struct RowFeeder {
         // one counter atomic hands out ~16 KB of rows: 1 chunk of 4 KB rows, 8 chunks of 512-B rows
         per_grab = 4096u / p.row_bytes;
         if (per_grab < 1) per_grab = 1;
-    }
-    __device__ __forceinline__ unsigned grab() {
-        if (blk_left == 0) {
-            if (dry) return n_chunks;
-            unsigned base = 0;
-            if (lane == 0) base = atomicAdd(&wk->next, per_grab);
-            base = __shfl_sync(0xffffffffu, base, 0);
-            if (base >= n_chunks) { dry = true; return n_chunks; }
-            blk_next = base;
-            blk_left = per_grab;
-        }
-        blk_left--;
-        const unsigned c = blk_next++;
-        return c < n_chunks ? c : n_chunks;
+        first_dyn = gridDim.x * (blockDim.x >> 5);
     }
     __device__ __forceinline__ void load_ids(unsigned c, uint64_t& id, int& g, uint32_t& set) const {
         id = 0; g = p.my_slot; set = 0;
@@ -321,30 +307,49 @@ struct RowFeeder {
         }
     }
     __device__ __forceinline__ void start() {
-        cA = grab(); cB = grab(); cC = grab();
+        const unsigned w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+        cA = w < n_chunks ? w : n_chunks;
+        cB = n_chunks;
         load_ids(cA, idA, gA, setA);
-        load_ids(cB, idB, gB, setB);
         probe(cA, idA, gA, setA, tA);
     }
     __device__ __forceinline__ bool have() const { return cA < n_chunks; }
-    // issue the loads of the stages behind chunk A (call before copying A's rows)
-    __device__ __forceinline__ unsigned prefetch() {
-        probe(cB, idB, gB, setB, tB);
-        load_ids(cC, idC, gC, setC);
-        return grab();
+    // step 1 of opening the next chunk: the counter atomic (only when the block handed out last is used up)
+    __device__ __forceinline__ void claim() {
+        claimed = false;
+        if (blk_left == 0 && !dry) {
+            if (lane == 0) raw = atomicAdd(&wk->next, per_grab);
+            claimed = true;
+        }
     }
-    __device__ __forceinline__ void rotate(unsigned cD) {
+    // step 2: the chunk's index is known -> its id loads
+    __device__ __forceinline__ void fetch_ids() {
+        if (claimed) {
+            const unsigned base = __shfl_sync(0xffffffffu, raw, 0);
+            if (base >= n_chunks || first_dyn + base >= n_chunks) dry = true;
+            else { blk_next = first_dyn + base; blk_left = per_grab; }
+        }
+        cB = n_chunks;
+        if (blk_left) {
+            blk_left--;
+            const unsigned c = blk_next++;
+            if (c < n_chunks) cB = c;
+        }
+        load_ids(cB, idB, gB, setB);
+    }
+    // step 3: its tag probes
+    __device__ __forceinline__ void probe_next() { probe(cB, idB, gB, setB, tB); }
+    __device__ __forceinline__ void rotate() {
         cA = cB; idA = idB; gA = gB; setA = setB;
 #pragma unroll
         for (int i = 0; i < GATHER_CH; i++) tA[i] = tB[i];
-        cB = cC; idB = idC; gB = gC; setB = setC;
-        cC = cD;
     }
     __device__ __forceinline__ int rows_in_A() const {
         const int64_t left = n - (int64_t)cA * GATHER_CH;
         return left < GATHER_CH ? (int)left : GATHER_CH;
     }
 };
+static_assert(GATHER_CH >= 3, "the three front-end steps of the next chunk are interleaved with the rows of the current one");
 
 // the last CTA out re-arms the work counter for a later launch that gets the same pool entry
 __device__ __forceinline__ void gather_work_done(GatherWork* wk) {
@@ -359,42 +364,93 @@ __device__ __forceinline__ void gather_work_done(GatherWork* wk) {
     }
 }
 
+// A hit row whose deferred re-check failed goes back through the full protocol with a fresh probe (rare: out of line).
+template <int VPL, bool SYS>
+__device__ __noinline__ int redo_row(const CacheParams& p, uint64_t tw, float* out_row, unsigned lane) {
+    const uint64_t id = tw & TAG_ID_MASK;
+    const int g = p.route_gpus > 1 ? (int)(id % (uint64_t)p.route_gpus) : p.my_slot;
+    const uint32_t set = (uint32_t)((id / (uint64_t)p.hash_div) % p.num_sets);
+    const uint64_t t = ld_relaxed_u64<SYS>(p.shard[g].tags + (uint64_t)set * COALA_WAYS + lane);
+    return resolve_row<VPL, SYS>(p, id, g, set, t, out_row, lane);
+}
+
+// Register-path gather.  A hit row costs ONE exposed memory latency: the seqlock re-check of row i (issued once row i's
+// words have arrived - its address depends on them) is only looked at after the loads of the NEXT hit row are in flight.
+// Until then row i sits in the output unvalidated; if the re-check then fails (a writer refilled the line under the
+// copy: rare) the row is redone through resolve_row, which rewrites it.  What is carried across rows is five registers
+// (the two tag observations and the row number); id, owner and set of a failed row are recomputed from its tag.
 template <int VPL, bool SYS>
 __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_kernel(const __grid_constant__ CacheParams p, const int64_t* __restrict__ idx,
-                                                              float* __restrict__ out, int64_t n,
-                                                              const int64_t* __restrict__ n_dev, GatherWork* wk) {
+                                                                 float* __restrict__ out, int64_t n,
+                                                                 const int64_t* __restrict__ n_dev, GatherWork* wk) {
     __shared__ unsigned s_stat[3];
     if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
     __syncthreads();
     if (n_dev) n = min(n, *n_dev);
     const unsigned lane = lane_id();
+    const uint32_t row_vecs = p.row_bytes >> 4;
     unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
+    uint64_t pend_t2 = 0, pend_tw = 0;   // re-check of the last hit row: observed tag, expected tag
+    uint32_t pend_row = 0;
+    bool pend = false;
+    auto redo = [&](uint64_t tw, uint32_t row) {
+        const int res = redo_row<VPL, SYS>(p, tw, out + (int64_t)row * (int64_t)p.out_stride, lane);
+        n_hit += (res == 0) - 1;   // it had been counted as a hit
+        n_miss += res == 1;
+        n_byp += res == 2;
+    };
     RowFeeder<SYS> f(p, idx, n, wk, lane);
     f.start();
     while (f.have()) {
-        const unsigned cD = f.prefetch();
         const int cnt = f.rows_in_A();
         const int64_t base = (int64_t)f.cA * GATHER_CH;
 #pragma unroll
         for (int i = 0; i < GATHER_CH; i++) {
+            if (i == 0) f.claim();
+            if (i == 1) f.fetch_ids();
+            if (i == 2) f.probe_next();
             if (i < cnt) {
                 const uint64_t id = __shfl_sync(0xffffffffu, f.idA, i);
                 const int g = __shfl_sync(0xffffffffu, f.gA, i);
                 const uint32_t set = __shfl_sync(0xffffffffu, f.setA, i);
+                const uint64_t t = f.tA[i];
                 float* out_row = out + (base + i) * (int64_t)p.out_stride;
-                if (id < p.id_limit) {
-                    const int res = resolve_row<VPL, SYS>(p, id, g, set, f.tA[i], out_row, lane);
+                if (id >= p.id_limit) {
+                    refuse_row(p, out_row, lane);
+                    n_bad++;
+                    continue;
+                }
+                const unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
+                const int way = m ? __ffs(m) - 1 : 0;
+                const uint64_t tw = __shfl_sync(0xffffffffu, t, way);
+                if (m && ((tw >> TAG_VER_SHIFT) & 1) == 0) {
+                    const ShardView& sh = p.shard[g];
+                    const uint64_t slot = (uint64_t)set * COALA_WAYS + way;
+                    const uint4* src = sh.lines + slot * row_vecs;
+                    uint4 v[VPL];
+#pragma unroll
+                    for (int k = 0; k < VPL; k++) v[k] = ld_line_v4<SYS>(src + k * 32 + lane);
+                    // the previous hit row's re-check was issued before these loads: it is back first
+                    const bool bad = pend && !__all_sync(0xffffffffu, pend_t2 == pend_tw);
+                    store_out_row<VPL>(p, out_row, v, lane);
+                    uint32_t acc = 0;
+#pragma unroll
+                    for (int k = 0; k < VPL; k++) acc |= v[k].x | v[k].y | v[k].z | v[k].w;
+                    const uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + slot + (acc & p.zero));
+                    if (bad) redo(pend_tw, pend_row);
+                    pend_t2 = t2; pend_tw = tw; pend_row = (uint32_t)(base + i); pend = true;
+                    n_hit++;
+                } else {
+                    const int res = resolve_row<VPL, SYS>(p, id, g, set, t, out_row, lane);
                     n_hit += res == 0;
                     n_miss += res == 1;
                     n_byp += res == 2;
-                } else {
-                    refuse_row(p, out_row, lane);
-                    n_bad++;
                 }
             }
         }
-        f.rotate(cD);
+        f.rotate();
     }
+    if (pend && !__all_sync(0xffffffffu, pend_t2 == pend_tw)) redo(pend_tw, pend_row);
     if (lane == 0) {
         if (n_hit) atomicAdd(&s_stat[0], n_hit);
         if (n_miss) atomicAdd(&s_stat[1], n_miss);
@@ -451,7 +507,7 @@ struct BulkPending {   // a hit row whose line is on its way into shared memory
 };
 
 template <int VPL, bool SYS, int NBUF>
-__global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_bulk_kernel(const __grid_constant__ CacheParams p, const int64_t* __restrict__ idx,
+__global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(const __grid_constant__ CacheParams p, const int64_t* __restrict__ idx,
                                                                    float* __restrict__ out, int64_t n,
                                                                    const int64_t* __restrict__ n_dev, GatherWork* wk) {
     static_assert(NBUF == 2 || NBUF == 3, "queue below is written for one or two waiting rows");
@@ -500,11 +556,13 @@ __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_bulk_kernel(const __gr
     RowFeeder<SYS> f(p, idx, n, wk, lane);
     f.start();
     while (f.have()) {
-        const unsigned cD = f.prefetch();
         const int cnt = f.rows_in_A();
         const int64_t base = (int64_t)f.cA * GATHER_CH;
 #pragma unroll
         for (int i = 0; i < GATHER_CH; i++) {
+            if (i == 0) f.claim();
+            if (i == 1) f.fetch_ids();
+            if (i == 2) f.probe_next();
             if (i >= cnt) continue;
             const uint64_t id = __shfl_sync(0xffffffffu, f.idA, i);
             const int g = __shfl_sync(0xffffffffu, f.gA, i);
@@ -535,7 +593,7 @@ __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_bulk_kernel(const __gr
                 count(resolve_row_call<VPL, SYS>(p, id, g, set, t, out + (base + i) * (int64_t)p.out_stride, lane));
             }
         }
-        f.rotate(cD);
+        f.rotate();
     }
     while (waiting) complete_oldest();
     if (lane == 0) {

@@ -175,6 +175,19 @@ extern "C" int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int i
     return 0;
 }
 
+// classic peer access for plain cudaMalloc buffers of another GPU in this process (the cache shards do not need it:
+// they are VMM mappings); used by the link probes of scripts/
+extern "C" int coala_enable_peer_access(int device, int peer) {
+    COALA_CUDA(cudaSetDevice(device));
+    int can = 0;
+    COALA_CUDA(cudaDeviceCanAccessPeer(&can, device, peer));
+    if (!can) COALA_FAIL("peer access between these devices is not possible");
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer, 0);
+    if (e == cudaErrorPeerAccessAlreadyEnabled) { cudaGetLastError(); return 0; }
+    COALA_CUDA(e);
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------
 // row-gather probe: out[i] = table[idx[i]] for rows of `row_bytes`, NO cache protocol (no tags, no validation) - the
 // practical ceiling of the gather's access pattern on a link (local HBM, a peer's HBM, pinned host), against which the

@@ -285,6 +285,9 @@ int coala_synth_check_rows(uint64_t rows_ptr, uint64_t idx_ptr, int64_t n, int d
 /* streaming-read bandwidth probe of a device-visible range (host link / peer link / HBM peaks) */
 int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int iters, double* gb_per_s);
 
+/* cudaDeviceEnablePeerAccess(peer) on `device` (already enabled = success); for the link probes */
+int coala_enable_peer_access(int device, int peer);
+
 /* row-gather probe: out[i] = table[idx[i]] with no cache protocol - the practical ceiling of the gather's access pattern on
  * whatever link `table` sits behind (local HBM, a peer's HBM, pinned host).  idx holds iters * n ids (one list per timed
  * launch); rows_in_flight 1|2 per warp; ctas_per_sm CTAs of 256 threads per SM; returns the mean launch time (CUDA events). */

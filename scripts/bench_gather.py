@@ -220,8 +220,8 @@ if args.gpus >= 2:
     torch.cuda.set_device(1)
     peer_buf = torch.empty(1 << 30, dtype=torch.uint8, device="cuda:1")
     torch.cuda.set_device(0)
-    rc = torch.cuda.cudart().cudaDeviceEnablePeerAccess(1, 0)
-    if int(rc) in (0, 704):  # success | already enabled
+    rc = L.coala_enable_peer_access(0, 1)
+    if int(rc) == 0:
         torch.cuda.synchronize()
         check(L.coala_probe_read_bandwidth(peer_buf.data_ptr(), 1 << 30, 5, C.byref(gb)))
         res["nvlink_read_GBs"] = gb.value

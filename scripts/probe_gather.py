@@ -52,8 +52,8 @@ if args.gpus >= 2:
     torch.cuda.set_device(1)
     peer = torch.empty(n_rows * R, dtype=torch.uint8, device="cuda:1")
     torch.cuda.set_device(0)
-    rc = int(torch.cuda.cudart().cudaDeviceEnablePeerAccess(1, 0))
-    if rc in (0, 704):
+    rc = int(L.coala_enable_peer_access(0, 1))
+    if rc == 0:
         sweep("peer_hbm_nvlink", peer.data_ptr())
     else:
         res["peer_hbm_nvlink"] = "peer access unavailable (rc %d)" % rc

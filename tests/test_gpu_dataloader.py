@@ -130,3 +130,38 @@ def test_device_pipeline_two_stream_prefetch_is_bit_exact(tmp_path, backend, pre
         assert np.array_equal(rows.view(np.uint32), d["feat"][einp].view(np.uint32))
     g_ms = pipe.gather_ms()  # [mean CUDA-event time of the gather launches] from the native engine
     assert len(g_ms) == 1 and 0.0 < g_ms[0] < 50.0
+
+
+@pytest.mark.parametrize("backend", ["isolated", "nvshmem"])
+def test_papers100m_shaped_batch_gat_fanout_full_batch_size(tmp_path, backend):
+    """BASELINE config C4's regime at test size: 128-d rows (R = 512 B: one 16-byte vector per lane), three layers of
+    fan-out 10,10,10 at the full batch size of 1024 (up to 1.36 M rows per batch): rows bitwise equal to the table,
+    input nodes and every block equal to the oracle's, over batches that overflow a small cache."""
+    import torch
+    from COALA_GNN import Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
+    d = _dataset(tmp_path)  # 20 000 nodes x 128-d: a 10,10,10 batch of 1024 seeds touches most of the graph
+    B, fan = 1024, [10, 10, 10]
+    train = torch.from_numpy(synth.train_ids(d["n"], seed=2))
+    nd = Node_Distributor(d["comm"], train, B, *d["files"], parsing_method="node_color")
+    sampler = MultiLayerNeighborSampler(fan, seed=21)
+    loader = COALA_GNN_DataLoader(SSD_INFO(1, 512, 1024, 0), nd, d["g"], sampler, B, d["dim"], fan, 4, "cuda:0",  # 4 MB: 8192 lines < the ~19 K input nodes
+                                  cache_backend=backend, sim_buf=d["feat_uva"])
+    assert loader.COALA_GNN_Manager.max_sample_size == 1024 * 11 ** 3
+    indptr, indices, eids = d["csc"]
+    for step, (input_nodes, seeds, blocks, feat) in enumerate(loader):
+        if step >= 4:
+            break
+        torch.cuda.synchronize()
+        seeds_h = seeds.cpu().numpy()
+        assert np.array_equal(seeds_h, train.numpy()[step * B:(step + 1) * B])
+        einp, eout, eblocks = oracle.sample_blocks_detailed(indptr, indices, eids, seeds_h, fan, oracle.batch_key(21, step, 0))
+        assert np.array_equal(input_nodes.cpu().numpy(), einp)
+        assert len(blocks) == 3
+        for b, e in zip(blocks, eblocks):
+            assert np.array_equal(b.src_nodes.cpu().numpy(), e["src_nodes"]) and np.array_equal(b.edge_src.cpu().numpy(), e["edge_src"])
+            assert np.array_equal(b.edge_dst.cpu().numpy(), e["edge_dst"]) and np.array_equal(b.edge_id.cpu().numpy(), e["edge_id"])
+        rows = feat.cpu().numpy()
+        assert rows.shape == (len(einp), d["dim"])
+        assert np.array_equal(rows.view(np.uint32), d["feat"][einp].view(np.uint32))
+    h, m, b = loader.COALA_GNN_Manager.COALA_GNN_Cache.stats()
+    assert m > 0 and h + m + b > 0
