@@ -51,6 +51,8 @@ struct CacheParams {
     unsigned long long* stats;  // [0]=hit [1]=miss [2]=bypass [3]=ids refused (>= id_limit)
     uint64_t id_limit;       // ids >= id_limit are refused: min(rows of the host table, 2^40 - 1 = the tag's id field)
     uint32_t zero;           // always 0 at run time; unknown to the compiler (see read_line_validated)
+    unsigned* miss_hint;     // [0] = rows the last finished launch did not find resident (drives the miss-prefetch pass)
+    int prefetch;            // miss-prefetch pass enabled (COALA_GATHER_PREFETCH, default 1)
 };
 
 constexpr int LOCK_TRIES = 64;     // CAS attempts on a set lock before bypassing
@@ -58,6 +60,7 @@ constexpr int BUSY_POLLS = 256;    // polls of a line being filled by someone el
 
 template <int VPL>
 __device__ __forceinline__ void store_out_row(const CacheParams& p, float* out_row, const uint4 (&v)[VPL], unsigned lane) {
+    if (!out_row) return;  // fill-only (miss-prefetch pass)
     if ((p.out_dim & 3) == 0 && (p.out_stride & 3) == 0) {
         const int nvec = p.out_dim >> 2;
 #pragma unroll
@@ -138,6 +141,26 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
             for (int k = 0; k < VPL; k++) acc |= v[k].x | v[k].y | v[k].z | v[k].w;
             const uint64_t t2 = ld_relaxed_u64<SYS>(sh.tags + slot0 + way + (acc & p.zero));
             if (__all_sync(0xffffffffu, t2 == tw)) return 0;
+        }
+    }
+
+    // ---- the line is being filled right now (id matches, odd version: typically by the miss-prefetch pass of this
+    // launch or by a peer): wait for the writer instead of fetching the same row from the host a second time
+    if (m) {
+        const int way = __ffs(m) - 1;
+        const uint64_t slot = slot0 + way;
+        uint64_t tw = __shfl_sync(0xffffffffu, t, way);
+#pragma unroll 1
+        for (int poll = 0; poll < BUSY_POLLS && (tw & TAG_ID_MASK) == id; poll++) {
+            if (((tw >> TAG_VER_SHIFT) & 1) == 0) {
+                if (read_line_validated<VPL, SYS>(p, sh, slot, tw, row_vecs, v, lane)) {
+                    store_out_row<VPL>(p, out_row, v, lane);
+                    return 0;
+                }
+            } else {
+                __nanosleep(200);
+            }
+            tw = ld_relaxed_u64<SYS>(sh.tags + slot);
         }
     }
 
@@ -254,14 +277,18 @@ __device__ __forceinline__ void refuse_row(const CacheParams& p, float* out_row,
 // has a row's copy time to complete and a warp never holds more than one unprocessed chunk (what it claims ahead is what
 // it cannot give back when the list runs dry).  A tag probed one chunk early can be stale by the time it is used; it is
 // only a hint (the seqlock re-check / the probe under the set lock decide).
-constexpr int GATHER_CH = 4;
+constexpr int GATHER_CH = 3;
+constexpr int GS_SHIFT = 28;                       // owner index above the set index in one 32-bit word
+constexpr uint32_t GS_SET_MASK = (1u << GS_SHIFT) - 1;
 // Register cap of the register-path gather kernel: 2 resident CTAs x 256 threads x 96 = 48 K of the SM's 64 K registers,
 // which leaves a sampling CTA of another stream (256 threads x 54) room to be co-resident.
 #define GATHER_MAX_REGS 96
 
 struct GatherWork {       // one per in-flight launch (a small rotating pool per cache object)
     unsigned next;        // next dynamic chunk block to hand out (chunk index - number of warps in the grid)
-    unsigned done;        // CTAs that have finished (the last one re-arms both words for a later launch)
+    unsigned done;        // CTAs that have finished (the last one re-arms the words for a later launch)
+    unsigned absent;      // rows this launch did not find resident
+    unsigned pad;
 };
 
 template <bool SYS>
@@ -275,8 +302,7 @@ struct RowFeeder {
     bool dry = false, claimed = false;
     unsigned cA, cB;                     // chunk being copied, chunk being opened
     uint64_t idA = 0, idB = 0;
-    int gA = 0, gB = 0;
-    uint32_t setA = 0, setB = 0;
+    uint32_t gsA = 0, gsB = 0;           // owner << 28 | set  (num_sets < 2^28 is checked when the cache is created)
     uint64_t tA[GATHER_CH], tB[GATHER_CH];
 
     __device__ __forceinline__ RowFeeder(const CacheParams& p_, const int64_t* idx_, int64_t n_, GatherWork* wk_, unsigned lane_)
@@ -287,31 +313,31 @@ struct RowFeeder {
         if (per_grab < 1) per_grab = 1;
         first_dyn = gridDim.x * (blockDim.x >> 5);
     }
-    __device__ __forceinline__ void load_ids(unsigned c, uint64_t& id, int& g, uint32_t& set) const {
-        id = 0; g = p.my_slot; set = 0;
+    __device__ __forceinline__ void load_ids(unsigned c, uint64_t& id, uint32_t& gs) const {
+        id = 0; gs = (uint32_t)p.my_slot << GS_SHIFT;
         const int64_t row = (int64_t)c * GATHER_CH + lane;
         if (c < n_chunks && lane < GATHER_CH && row < n) {
             id = (uint64_t)__ldg(idx + row);
-            if (p.route_gpus > 1) g = (int)(id % (uint64_t)p.route_gpus);
-            set = (uint32_t)((id / (uint64_t)p.hash_div) % p.num_sets);
+            uint32_t g = (uint32_t)p.my_slot;
+            if (p.route_gpus > 1) g = (uint32_t)(id % (uint64_t)p.route_gpus);
+            gs = (g << GS_SHIFT) | (uint32_t)((id / (uint64_t)p.hash_div) % p.num_sets);
         }
     }
-    __device__ __forceinline__ void probe(unsigned c, uint64_t id, int g, uint32_t set, uint64_t (&t)[GATHER_CH]) const {
+    __device__ __forceinline__ void probe(unsigned c, uint32_t gs, uint64_t (&t)[GATHER_CH]) const {
 #pragma unroll
         for (int i = 0; i < GATHER_CH; i++) {
-            const int gi = __shfl_sync(0xffffffffu, g, i);
-            const uint32_t si = __shfl_sync(0xffffffffu, set, i);
+            const uint32_t x = __shfl_sync(0xffffffffu, gs, i);
             t[i] = 0;
             if (c < n_chunks && (int64_t)c * GATHER_CH + i < n)
-                t[i] = ld_relaxed_u64<SYS>(p.shard[gi].tags + (uint64_t)si * COALA_WAYS + lane);
+                t[i] = ld_relaxed_u64<SYS>(p.shard[x >> GS_SHIFT].tags + (uint64_t)(x & GS_SET_MASK) * COALA_WAYS + lane);
         }
     }
     __device__ __forceinline__ void start() {
         const unsigned w = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
         cA = w < n_chunks ? w : n_chunks;
         cB = n_chunks;
-        load_ids(cA, idA, gA, setA);
-        probe(cA, idA, gA, setA, tA);
+        load_ids(cA, idA, gsA);
+        probe(cA, gsA, tA);
     }
     __device__ __forceinline__ bool have() const { return cA < n_chunks; }
     // step 1 of opening the next chunk: the counter atomic (only when the block handed out last is used up)
@@ -335,12 +361,12 @@ struct RowFeeder {
             const unsigned c = blk_next++;
             if (c < n_chunks) cB = c;
         }
-        load_ids(cB, idB, gB, setB);
+        load_ids(cB, idB, gsB);
     }
     // step 3: its tag probes
-    __device__ __forceinline__ void probe_next() { probe(cB, idB, gB, setB, tB); }
+    __device__ __forceinline__ void probe_next() { probe(cB, gsB, tB); }
     __device__ __forceinline__ void rotate() {
-        cA = cB; idA = idB; gA = gB; setA = setB;
+        cA = cB; idA = idB; gsA = gsB;
 #pragma unroll
         for (int i = 0; i < GATHER_CH; i++) tA[i] = tB[i];
     }
@@ -351,16 +377,72 @@ struct RowFeeder {
 };
 static_assert(GATHER_CH >= 3, "the three front-end steps of the next chunk are interleaved with the rows of the current one");
 
-// the last CTA out re-arms the work counter for a later launch that gets the same pool entry
-__device__ __forceinline__ void gather_work_done(GatherWork* wk) {
+// the last CTA out re-arms the work counter for a later launch that gets the same pool entry, and publishes how many rows
+// this launch did not find resident (s_stat[1] + s_stat[2] of every CTA) as the next launch's miss hint
+__device__ __forceinline__ void gather_work_done(const CacheParams& p, GatherWork* wk, const int* s_stat) {
     __syncthreads();
     if (threadIdx.x == 0) {
+        const int absent = s_stat[1] + s_stat[2];
+        if (absent > 0) atomicAdd(&wk->absent, (unsigned)absent);
         __threadfence();
         if (atomicAdd(&wk->done, 1u) == gridDim.x - 1) {
+            __threadfence();
+            if (gridDim.x > 1 || blockDim.x > 32) *p.miss_hint = *(volatile unsigned*)&wk->absent;  // (not the one-warp test launch)
             wk->next = 0;
             wk->done = 0;
+            wk->absent = 0;
             __threadfence();
         }
+    }
+}
+
+// Miss-prefetch pass (longest job first).  A miss costs ~10x a hit in warp time (host read + set lock + fill, over NVLink
+// when the owner is a peer), and rows met late in the queue made the launch end with most warps idle behind a few fills
+// (27 % of all warp time at the final barrier with 3 % misses, profiles/r2_gather_miss03_before.txt).  So before the copy
+// loop every warp probes the tags of its own 1/W-th of the list, several probes in flight, and FILLS what is absent (no
+// output).  All host reads of the launch are then in flight within the first microseconds - the host link is busy from the
+// start - and the copy loop, whose queue balances whatever is left, finds the rows resident (or being filled: it waits for
+// the writer).  Rows filled here are counted as misses; the hit the copy loop will report for them is taken back, so
+// hit + miss + bypass stays equal to the number of requests.  Skipped when the previous launch found everything resident.
+template <int VPL, bool SYS>
+__device__ __noinline__ void miss_prefetch(const CacheParams& p, const int64_t* __restrict__ idx, int64_t n, unsigned lane, int* s_stat) {
+    const int64_t W = (int64_t)gridDim.x * (blockDim.x >> 5);
+    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const int64_t span = (n + W - 1) / W;
+    const int64_t r1 = min(n, (w + 1) * span);
+    int filled = 0;
+    for (int64_t r0 = w * span; r0 < r1; r0 += 32) {
+        const int cnt = (int)min((int64_t)32, r1 - r0);
+        uint64_t my_id = 0;
+        uint32_t my_gs = (uint32_t)p.my_slot << GS_SHIFT;
+        if ((int)lane < cnt) {
+            my_id = (uint64_t)__ldg(idx + r0 + lane);
+            uint32_t g = (uint32_t)p.my_slot;
+            if (p.route_gpus > 1) g = (uint32_t)(my_id % (uint64_t)p.route_gpus);
+            my_gs = (g << GS_SHIFT) | (uint32_t)((my_id / (uint64_t)p.hash_div) % p.num_sets);
+        }
+        for (int j = 0; j < cnt; j += 4) {
+            uint64_t t[4];
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t x = __shfl_sync(0xffffffffu, my_gs, (j + u) & 31);
+                t[u] = 0;
+                if (j + u < cnt) t[u] = ld_relaxed_u64<SYS>(p.shard[x >> GS_SHIFT].tags + (uint64_t)(x & GS_SET_MASK) * COALA_WAYS + lane);
+            }
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                if (j + u < cnt) {
+                    const uint64_t id = __shfl_sync(0xffffffffu, my_id, j + u);
+                    const uint32_t x = __shfl_sync(0xffffffffu, my_gs, j + u);
+                    if (id < p.id_limit && __ballot_sync(0xffffffffu, (t[u] & TAG_ID_MASK) == id) == 0)
+                        filled += resolve_row<VPL, SYS>(p, id, (int)(x >> GS_SHIFT), x & GS_SET_MASK, t[u], nullptr, lane) == 1;
+                }
+            }
+        }
+    }
+    if (lane == 0 && filled) {
+        atomicAdd(&s_stat[1], filled);
+        atomicSub(&s_stat[0], filled);
     }
 }
 
@@ -383,21 +465,21 @@ template <int VPL, bool SYS>
 __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_kernel(const __grid_constant__ CacheParams p, const int64_t* __restrict__ idx,
                                                                  float* __restrict__ out, int64_t n,
                                                                  const int64_t* __restrict__ n_dev, GatherWork* wk) {
-    __shared__ unsigned s_stat[3];
+    __shared__ int s_stat[3];
     if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
     __syncthreads();
     if (n_dev) n = min(n, *n_dev);
     const unsigned lane = lane_id();
     const uint32_t row_vecs = p.row_bytes >> 4;
-    unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
+    if (p.prefetch && blockDim.x > 32 && *(volatile unsigned*)p.miss_hint != 0) miss_prefetch<VPL, SYS>(p, idx, n, lane, s_stat);
+    unsigned n_hit = 0;   // misses, bypasses and refused ids are rare: counted straight into shared / global memory
     uint64_t pend_t2 = 0, pend_tw = 0;   // re-check of the last hit row: observed tag, expected tag
     uint32_t pend_row = 0;
     bool pend = false;
     auto redo = [&](uint64_t tw, uint32_t row) {
         const int res = redo_row<VPL, SYS>(p, tw, out + (int64_t)row * (int64_t)p.out_stride, lane);
         n_hit += (res == 0) - 1;   // it had been counted as a hit
-        n_miss += res == 1;
-        n_byp += res == 2;
+        if (res && lane == 0) atomicAdd(&s_stat[res], 1);
     };
     RowFeeder<SYS> f(p, idx, n, wk, lane);
     f.start();
@@ -411,13 +493,14 @@ __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_kernel(const __grid_co
             if (i == 2) f.probe_next();
             if (i < cnt) {
                 const uint64_t id = __shfl_sync(0xffffffffu, f.idA, i);
-                const int g = __shfl_sync(0xffffffffu, f.gA, i);
-                const uint32_t set = __shfl_sync(0xffffffffu, f.setA, i);
+                const uint32_t gs = __shfl_sync(0xffffffffu, f.gsA, i);
+                const int g = (int)(gs >> GS_SHIFT);
+                const uint32_t set = gs & GS_SET_MASK;
                 const uint64_t t = f.tA[i];
                 float* out_row = out + (base + i) * (int64_t)p.out_stride;
                 if (id >= p.id_limit) {
                     refuse_row(p, out_row, lane);
-                    n_bad++;
+                    if (lane == 0) atomicAdd(p.stats + 3, 1ULL);
                     continue;
                 }
                 const unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
@@ -443,23 +526,17 @@ __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_kernel(const __grid_co
                 } else {
                     const int res = resolve_row<VPL, SYS>(p, id, g, set, t, out_row, lane);
                     n_hit += res == 0;
-                    n_miss += res == 1;
-                    n_byp += res == 2;
+                    if (res && lane == 0) atomicAdd(&s_stat[res], 1);
                 }
             }
         }
         f.rotate();
     }
     if (pend && !__all_sync(0xffffffffu, pend_t2 == pend_tw)) redo(pend_tw, pend_row);
-    if (lane == 0) {
-        if (n_hit) atomicAdd(&s_stat[0], n_hit);
-        if (n_miss) atomicAdd(&s_stat[1], n_miss);
-        if (n_byp) atomicAdd(&s_stat[2], n_byp);
-        if (n_bad) atomicAdd(p.stats + 3, (unsigned long long)n_bad);
-    }
+    if (lane == 0 && n_hit) atomicAdd(&s_stat[0], (int)n_hit);
     __syncthreads();
-    if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
-    gather_work_done(wk);
+    if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)(long long)s_stat[threadIdx.x]);
+    gather_work_done(p, wk, s_stat);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -513,7 +590,7 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(const __grid_
     static_assert(NBUF == 2 || NBUF == 3, "queue below is written for one or two waiting rows");
     extern __shared__ __align__(128) uint8_t dyn_smem[];
     __shared__ uint64_t bars[8][NBUF];
-    __shared__ unsigned s_stat[3];
+    __shared__ int s_stat[3];
     const unsigned lane = lane_id();
     const int wib = threadIdx.x >> 5;
     uint8_t* mybuf = dyn_smem + (size_t)wib * NBUF * p.row_bytes;
@@ -525,6 +602,7 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(const __grid_
     }
     __syncthreads();
     if (n_dev) n = min(n, *n_dev);
+    if (p.prefetch && *(volatile unsigned*)p.miss_hint != 0) miss_prefetch<VPL, SYS>(p, idx, n, lane, s_stat);
     const uint32_t out_bytes = (uint32_t)p.out_dim * 4;
     unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
     unsigned phase_bits = 0;   // bit b = parity the next wait on buffer b expects
@@ -565,8 +643,9 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(const __grid_
             if (i == 2) f.probe_next();
             if (i >= cnt) continue;
             const uint64_t id = __shfl_sync(0xffffffffu, f.idA, i);
-            const int g = __shfl_sync(0xffffffffu, f.gA, i);
-            const uint32_t set = __shfl_sync(0xffffffffu, f.setA, i);
+            const uint32_t gs = __shfl_sync(0xffffffffu, f.gsA, i);
+            const int g = (int)(gs >> GS_SHIFT);
+            const uint32_t set = gs & GS_SET_MASK;
             const uint64_t t = f.tA[i];
             const unsigned m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
             const unsigned way = m ? __ffs(m) - 1 : 0;
@@ -598,12 +677,12 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(const __grid_
     while (waiting) complete_oldest();
     if (lane == 0) {
         bulk_wait_all();
-        if (n_hit) atomicAdd(&s_stat[0], n_hit);
-        if (n_miss) atomicAdd(&s_stat[1], n_miss);
-        if (n_byp) atomicAdd(&s_stat[2], n_byp);
+        if (n_hit) atomicAdd(&s_stat[0], (int)n_hit);
+        if (n_miss) atomicAdd(&s_stat[1], (int)n_miss);
+        if (n_byp) atomicAdd(&s_stat[2], (int)n_byp);
         if (n_bad) atomicAdd(p.stats + 3, (unsigned long long)n_bad);
     }
     __syncthreads();
-    if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)s_stat[threadIdx.x]);
-    gather_work_done(wk);
+    if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)(long long)s_stat[threadIdx.x]);
+    gather_work_done(p, wk, s_stat);
 }
