@@ -65,8 +65,6 @@ struct coala_cache {
     int sm_count = 148;
     GatherWork* d_work = nullptr;  // rotating pool of device-side work counters (one per in-flight launch)
     unsigned launch_seq = 0;
-    unsigned* d_hint = nullptr;    // device word: rows the last launch did not find resident (0 = skip the miss-prefetch pass)
-    bool prefetch_pass = true;
     std::vector<int32_t> h_counters;
 };
 
@@ -218,12 +216,6 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     COALA_CUDA_NULL(cudaMemset(c->d_stats, 0, 4 * sizeof(unsigned long long)));
     COALA_CUDA_NULL(cudaMalloc(&c->d_work, GATHER_WORK_POOL * sizeof(GatherWork)));
     COALA_CUDA_NULL(cudaMemset(c->d_work, 0, GATHER_WORK_POOL * sizeof(GatherWork)));
-    COALA_CUDA_NULL(cudaMalloc(&c->d_hint, sizeof(unsigned)));
-    {
-        unsigned one = 1;  // a cold cache: the first launch runs the miss-prefetch pass (COALA_GATHER_PREFETCH=0 disables the pass)
-        if (const char* e = getenv("COALA_GATHER_PREFETCH")) c->prefetch_pass = atoi(e) != 0;
-        COALA_CUDA_NULL(cudaMemcpy(c->d_hint, &one, sizeof(one), cudaMemcpyHostToDevice));
-    }
 
     CacheParams& p = c->params;
     memset(&p, 0, sizeof(p));
@@ -239,8 +231,8 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     p.out_stride = feat_dim;
     p.out_dim = feat_dim < cache_dim ? feat_dim : cache_dim;
     p.stats = c->d_stats;
-    p.miss_hint = c->d_hint;
-    p.prefetch = c->prefetch_pass ? 1 : 0;
+    p.fenced = 0;
+    if (const char* e = getenv("COALA_CACHE_FENCED")) p.fenced = atoi(e) != 0;
     p.zero = 0;
     // ids are bounds-checked on the device: against the tag's id field always, against the table's row count as
     // soon as it is known (from the distributor's colour table, or coala_cache_set_num_nodes)
@@ -271,7 +263,6 @@ extern "C" void coala_cache_destroy(coala_cache* c) {
     else if (c->slab) cudaFree(c->slab);
     if (c->d_stats) cudaFree(c->d_stats);
     if (c->d_work) cudaFree(c->d_work);
-    if (c->d_hint) cudaFree(c->d_hint);
     delete c;
 }
 

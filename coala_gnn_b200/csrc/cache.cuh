@@ -51,8 +51,7 @@ struct CacheParams {
     unsigned long long* stats;  // [0]=hit [1]=miss [2]=bypass [3]=ids refused (>= id_limit)
     uint64_t id_limit;       // ids >= id_limit are refused: min(rows of the host table, 2^40 - 1 = the tag's id field)
     uint32_t zero;           // always 0 at run time; unknown to the compiler (see read_line_validated)
-    unsigned* miss_hint;     // [0] = rows the last finished launch did not find resident (drives the miss-prefetch pass)
-    int prefetch;            // miss-prefetch pass enabled (COALA_GATHER_PREFETCH, default 1)
+    int fenced;              // 1: writers order their stores with fence.acq_rel (PTX-model-exact); 0: by read-back + dependency
 };
 
 constexpr int LOCK_TRIES = 64;     // CAS attempts on a set lock before bypassing
@@ -60,7 +59,6 @@ constexpr int BUSY_POLLS = 256;    // polls of a line being filled by someone el
 
 template <int VPL>
 __device__ __forceinline__ void store_out_row(const CacheParams& p, float* out_row, const uint4 (&v)[VPL], unsigned lane) {
-    if (!out_row) return;  // fill-only (miss-prefetch pass)
     if ((p.out_dim & 3) == 0 && (p.out_stride & 3) == 0) {
         const int nvec = p.out_dim >> 2;
 #pragma unroll
@@ -144,8 +142,8 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
         }
     }
 
-    // ---- the line is being filled right now (id matches, odd version: typically by the miss-prefetch pass of this
-    // launch or by a peer): wait for the writer instead of fetching the same row from the host a second time
+    // ---- the line is being filled right now (id matches, odd version: by another warp of this launch
+    // or by a peer): wait for the writer instead of fetching the same row from the host a second time
     if (m) {
         const int way = __ffs(m) - 1;
         const uint64_t slot = slot0 + way;
@@ -168,6 +166,17 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
     // table is immutable so the registers are valid whatever happens to the line meanwhile.
     load_host_row<VPL>(p, id, v, lane);
 
+    // Writer-side ordering.  The protocol needs three orders: (a) the lock is taken before the set is re-probed, (b) the
+    // busy tag is in place before the unlock and before any line word changes, (c) every line word is in place before the
+    // tag turns even again.  With p.fenced they are PTX acquire / release / fence.acq_rel (MEMBAR.{GPU,SYS}).  Measured on
+    // B200 a system-scope MEMBAR in this kernel completes in ~20 us (it waits for every access the thread has in flight,
+    // the host-row loads over PCIe included): three per fill put the launch's critical path into a handful of late
+    // misses (profiles/r2_gather_miss03_before.txt: 8 % of all warp time in MEMBAR, 27 % idle at the final barrier behind
+    // it).  Default (p.fenced == 0): the same orders by READ-BACK + register dependency, like the reader side - all of
+    // these are strong accesses that resolve at the owner's L2, the single coherence point of the shard: a strong load of
+    // the word just stored returns only once that store is performed there (same-address order), and an access whose
+    // address depends on the returned value is issued after it.  Two round trips to the owner's L2 per fill, no MEMBAR.
+    const bool fenced = p.fenced != 0;
     uint64_t s = 0;
     bool locked = false;
     if (lane == 0) {
@@ -175,7 +184,10 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
 #pragma unroll 1
         for (int tries = 0; tries < LOCK_TRIES; tries++) {
             s = ld_relaxed_u64<SYS>(sh.set_seq + set);
-            if ((s & 1) == 0 && cas_acquire_u64<SYS>(sh.set_seq + set, s, s + 1) == s) { locked = true; break; }
+            if ((s & 1) == 0 && (fenced ? cas_acquire_u64<SYS>(sh.set_seq + set, s, s + 1) : cas_relaxed_u64<SYS>(sh.set_seq + set, s, s + 1)) == s) {
+                locked = true;
+                break;
+            }
             __nanosleep(ns);
             if (ns < 1024) ns <<= 1;
         }
@@ -187,13 +199,17 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
         return 2;
     }
 
-    // ---- under the set lock: re-probe (someone may have filled it since the optimistic probe)
-    t = ld_acquire_u64<SYS>(sh.tags + slot0 + lane);
+    // ---- under the set lock: re-probe (someone may have filled it since the optimistic probe).  (a): the probe's
+    // address depends on the value the CAS returned.
+    t = fenced ? ld_acquire_u64<SYS>(sh.tags + slot0 + lane) : ld_relaxed_u64<SYS>(sh.tags + slot0 + lane + ((uint32_t)s & p.zero));
     m = __ballot_sync(0xffffffffu, (t & TAG_ID_MASK) == id);
     if (m) {
         // present (possibly still being filled by another warp / GPU): nothing to modify,
         // so restore the even value — readers that sampled `s` stay valid, no way is consumed.
-        if (lane == 0) st_release_u64<SYS>(sh.set_seq + set, s);
+        if (lane == 0) {
+            if (fenced) st_release_u64<SYS>(sh.set_seq + set, s);
+            else st_relaxed_u64<SYS>(sh.set_seq + set, s);
+        }
         int way = __ffs(m) - 1;
         const uint64_t slot = slot0 + way;
         uint64_t tw = __shfl_sync(0xffffffffu, t, way);
@@ -208,7 +224,7 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
             } else {
                 __nanosleep(256);
             }
-            tw = ld_acquire_u64<SYS>(sh.tags + slot);
+            tw = ld_relaxed_u64<SYS>(sh.tags + slot);
         }
         load_host_row<VPL>(p, id, v, lane);  // registers were reused for the line: host copy is bit-identical
         store_out_row<VPL>(p, out_row, v, lane);
@@ -220,34 +236,62 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
     const uint64_t slot = slot0 + way;
     const uint64_t told = __shfl_sync(0xffffffffu, t, way);
     if ((told >> TAG_VER_SHIFT) & 1) {  // victim is still being filled by a writer 32 fills ago
-        if (lane == 0) st_release_u64<SYS>(sh.set_seq + set, s);
+        if (lane == 0) {
+            if (fenced) st_release_u64<SYS>(sh.set_seq + set, s);
+            else st_relaxed_u64<SYS>(sh.set_seq + set, s);
+        }
         store_out_row<VPL>(p, out_row, v, lane);
         return 2;
     }
     const uint64_t ver = (told >> TAG_VER_SHIFT) + 1;  // odd: line busy
+    uint32_t dep = 0;
     if (lane == 0) {
-        st_relaxed_u64<SYS>(sh.tags + slot, (ver << TAG_VER_SHIFT) | id);
+        const uint64_t busy = (ver << TAG_VER_SHIFT) | id;
+        st_relaxed_u64<SYS>(sh.tags + slot, busy);
         if (p.track_color) {  // M/isolated_cache.h:432-446
-            uint32_t oldc = sh.color_meta[slot];
+            // strong accesses: the slot's previous filler may have been another SM or GPU (no acquire invalidates L1 here)
+            uint32_t oldc = ld_relaxed_u32<SYS>(sh.color_meta + slot);
             uint32_t newc = (uint32_t)p.color[id];
-            sh.color_meta[slot] = newc;
+            st_relaxed_u32<SYS>(sh.color_meta + slot, newc);
             red_add_s32<SYS>(sh.color_counters + oldc, -1);
             red_add_s32<SYS>(sh.color_counters + newc, 1);
         }
-        st_release_u64<SYS>(sh.set_seq + set, s + 2);  // unlock; the line stays busy via its tag
-        fence_acq_rel<SYS>();                            // busy tag visible before any line data
+        if (fenced) {
+            st_release_u64<SYS>(sh.set_seq + set, s + 2);  // unlock; the line stays busy via its tag
+            fence_acq_rel<SYS>();                            // busy tag visible before any line data
+        } else {
+            // (b): the busy tag is read back from the owner's L2; the unlock and (through `dep`) every line store depend on it
+            // (the colour word of the slot is read back with it: the slot's next filler reads it under the lock)
+            const uint64_t tb = ld_relaxed_u64<SYS>(sh.tags + slot);
+            const uint32_t cb = p.track_color ? ld_relaxed_u32<SYS>(sh.color_meta + slot) : 0u;
+            dep = ((uint32_t)tb | cb) & p.zero;
+            st_relaxed_u64<SYS>(sh.set_seq + set, s + 2 + dep);
+        }
     }
+    dep = __shfl_sync(0xffffffffu, dep, 0);
     __syncwarp();
 
     // ---- fill: host row -> line and -> output from the same registers
-    uint4* dst = sh.lines + slot * row_vecs;
+    uint4* dst = sh.lines + slot * row_vecs + dep;
 #pragma unroll
     for (int k = 0; k < VPL; k++) st_line_v4<SYS>(dst + k * 32 + lane, v[k]);
     store_out_row<VPL>(p, out_row, v, lane);
-    __syncwarp();
-    if (lane == 0) {
-        fence_acq_rel<SYS>();  // cumulative: the whole warp's line stores precede the publish
-        st_relaxed_u64<SYS>(sh.tags + slot, ((ver + 1) << TAG_VER_SHIFT) | id);
+    if (fenced) {
+        __syncwarp();
+        if (lane == 0) {
+            fence_acq_rel<SYS>();  // cumulative: the whole warp's line stores precede the publish
+            st_relaxed_u64<SYS>(sh.tags + slot, ((ver + 1) << TAG_VER_SHIFT) | id);
+        }
+    } else {
+        // (c): every lane reads its line words back; the publish depends on all of them through the ballot
+        uint32_t acc = 0;
+#pragma unroll
+        for (int k = 0; k < VPL; k++) {
+            const uint4 r = ld_line_v4<SYS>(dst + k * 32 + lane);
+            acc |= r.x | r.y | r.z | r.w;
+        }
+        const unsigned all = __ballot_sync(0xffffffffu, (acc & p.zero) != 0);  // 0, known only when every lane's words are back
+        if (lane == 0) st_relaxed_u64<SYS>(sh.tags + slot, (((ver + 1) << TAG_VER_SHIFT) | id) + all);
     }
     return 1;
 }
@@ -286,9 +330,7 @@ constexpr uint32_t GS_SET_MASK = (1u << GS_SHIFT) - 1;
 
 struct GatherWork {       // one per in-flight launch (a small rotating pool per cache object)
     unsigned next;        // next dynamic chunk block to hand out (chunk index - number of warps in the grid)
-    unsigned done;        // CTAs that have finished (the last one re-arms the words for a later launch)
-    unsigned absent;      // rows this launch did not find resident
-    unsigned pad;
+    unsigned done;        // CTAs that have finished (the last one re-arms both words for a later launch)
 };
 
 template <bool SYS>
@@ -377,72 +419,16 @@ struct RowFeeder {
 };
 static_assert(GATHER_CH >= 3, "the three front-end steps of the next chunk are interleaved with the rows of the current one");
 
-// the last CTA out re-arms the work counter for a later launch that gets the same pool entry, and publishes how many rows
-// this launch did not find resident (s_stat[1] + s_stat[2] of every CTA) as the next launch's miss hint
-__device__ __forceinline__ void gather_work_done(const CacheParams& p, GatherWork* wk, const int* s_stat) {
+// the last CTA out re-arms the work counter for a later launch that gets the same pool entry
+__device__ __forceinline__ void gather_work_done(GatherWork* wk) {
     __syncthreads();
     if (threadIdx.x == 0) {
-        const int absent = s_stat[1] + s_stat[2];
-        if (absent > 0) atomicAdd(&wk->absent, (unsigned)absent);
         __threadfence();
         if (atomicAdd(&wk->done, 1u) == gridDim.x - 1) {
-            __threadfence();
-            if (gridDim.x > 1 || blockDim.x > 32) *p.miss_hint = *(volatile unsigned*)&wk->absent;  // (not the one-warp test launch)
             wk->next = 0;
             wk->done = 0;
-            wk->absent = 0;
             __threadfence();
         }
-    }
-}
-
-// Miss-prefetch pass (longest job first).  A miss costs ~10x a hit in warp time (host read + set lock + fill, over NVLink
-// when the owner is a peer), and rows met late in the queue made the launch end with most warps idle behind a few fills
-// (27 % of all warp time at the final barrier with 3 % misses, profiles/r2_gather_miss03_before.txt).  So before the copy
-// loop every warp probes the tags of its own 1/W-th of the list, several probes in flight, and FILLS what is absent (no
-// output).  All host reads of the launch are then in flight within the first microseconds - the host link is busy from the
-// start - and the copy loop, whose queue balances whatever is left, finds the rows resident (or being filled: it waits for
-// the writer).  Rows filled here are counted as misses; the hit the copy loop will report for them is taken back, so
-// hit + miss + bypass stays equal to the number of requests.  Skipped when the previous launch found everything resident.
-template <int VPL, bool SYS>
-__device__ __noinline__ void miss_prefetch(const CacheParams& p, const int64_t* __restrict__ idx, int64_t n, unsigned lane, int* s_stat) {
-    const int64_t W = (int64_t)gridDim.x * (blockDim.x >> 5);
-    const int64_t w = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const int64_t span = (n + W - 1) / W;
-    const int64_t r1 = min(n, (w + 1) * span);
-    int filled = 0;
-    for (int64_t r0 = w * span; r0 < r1; r0 += 32) {
-        const int cnt = (int)min((int64_t)32, r1 - r0);
-        uint64_t my_id = 0;
-        uint32_t my_gs = (uint32_t)p.my_slot << GS_SHIFT;
-        if ((int)lane < cnt) {
-            my_id = (uint64_t)__ldg(idx + r0 + lane);
-            uint32_t g = (uint32_t)p.my_slot;
-            if (p.route_gpus > 1) g = (uint32_t)(my_id % (uint64_t)p.route_gpus);
-            my_gs = (g << GS_SHIFT) | (uint32_t)((my_id / (uint64_t)p.hash_div) % p.num_sets);
-        }
-        for (int j = 0; j < cnt; j += 4) {
-            uint64_t t[4];
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                const uint32_t x = __shfl_sync(0xffffffffu, my_gs, (j + u) & 31);
-                t[u] = 0;
-                if (j + u < cnt) t[u] = ld_relaxed_u64<SYS>(p.shard[x >> GS_SHIFT].tags + (uint64_t)(x & GS_SET_MASK) * COALA_WAYS + lane);
-            }
-#pragma unroll
-            for (int u = 0; u < 4; u++) {
-                if (j + u < cnt) {
-                    const uint64_t id = __shfl_sync(0xffffffffu, my_id, j + u);
-                    const uint32_t x = __shfl_sync(0xffffffffu, my_gs, j + u);
-                    if (id < p.id_limit && __ballot_sync(0xffffffffu, (t[u] & TAG_ID_MASK) == id) == 0)
-                        filled += resolve_row<VPL, SYS>(p, id, (int)(x >> GS_SHIFT), x & GS_SET_MASK, t[u], nullptr, lane) == 1;
-                }
-            }
-        }
-    }
-    if (lane == 0 && filled) {
-        atomicAdd(&s_stat[1], filled);
-        atomicSub(&s_stat[0], filled);
     }
 }
 
@@ -471,7 +457,6 @@ __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_kernel(const __grid_co
     if (n_dev) n = min(n, *n_dev);
     const unsigned lane = lane_id();
     const uint32_t row_vecs = p.row_bytes >> 4;
-    if (p.prefetch && blockDim.x > 32 && *(volatile unsigned*)p.miss_hint != 0) miss_prefetch<VPL, SYS>(p, idx, n, lane, s_stat);
     unsigned n_hit = 0;   // misses, bypasses and refused ids are rare: counted straight into shared / global memory
     uint64_t pend_t2 = 0, pend_tw = 0;   // re-check of the last hit row: observed tag, expected tag
     uint32_t pend_row = 0;
@@ -536,7 +521,7 @@ __global__ void __maxnreg__(GATHER_MAX_REGS) coala_gather_kernel(const __grid_co
     if (lane == 0 && n_hit) atomicAdd(&s_stat[0], (int)n_hit);
     __syncthreads();
     if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)(long long)s_stat[threadIdx.x]);
-    gather_work_done(p, wk, s_stat);
+    gather_work_done(wk);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -602,7 +587,6 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(const __grid_
     }
     __syncthreads();
     if (n_dev) n = min(n, *n_dev);
-    if (p.prefetch && *(volatile unsigned*)p.miss_hint != 0) miss_prefetch<VPL, SYS>(p, idx, n, lane, s_stat);
     const uint32_t out_bytes = (uint32_t)p.out_dim * 4;
     unsigned n_hit = 0, n_miss = 0, n_byp = 0, n_bad = 0;
     unsigned phase_bits = 0;   // bit b = parity the next wait on buffer b expects
@@ -684,5 +668,5 @@ __global__ void __launch_bounds__(256, 2) coala_gather_bulk_kernel(const __grid_
     }
     __syncthreads();
     if (threadIdx.x < 3 && s_stat[threadIdx.x]) atomicAdd(p.stats + threadIdx.x, (unsigned long long)(long long)s_stat[threadIdx.x]);
-    gather_work_done(p, wk, s_stat);
+    gather_work_done(wk);
 }

@@ -71,6 +71,16 @@ template <bool SYS> __device__ __forceinline__ uint64_t ld_relaxed_u64(const uin
     else asm volatile("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
     return v;
 }
+template <bool SYS> __device__ __forceinline__ uint32_t ld_relaxed_u32(const uint32_t* p) {
+    uint32_t v;
+    if (SYS) asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    else asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+template <bool SYS> __device__ __forceinline__ void st_relaxed_u32(uint32_t* p, uint32_t v) {
+    if (SYS) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+    else asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 template <bool SYS> __device__ __forceinline__ void st_relaxed_u64(uint64_t* p, uint64_t v) {
     if (SYS) asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
     else asm volatile("st.relaxed.gpu.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
@@ -83,6 +93,12 @@ template <bool SYS> __device__ __forceinline__ uint64_t cas_acquire_u64(uint64_t
     uint64_t old;
     if (SYS) asm volatile("atom.acquire.sys.global.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "l"(p), "l"(cmp), "l"(val) : "memory");
     else asm volatile("atom.acquire.gpu.global.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "l"(p), "l"(cmp), "l"(val) : "memory");
+    return old;
+}
+template <bool SYS> __device__ __forceinline__ uint64_t cas_relaxed_u64(uint64_t* p, uint64_t cmp, uint64_t val) {
+    uint64_t old;
+    if (SYS) asm volatile("atom.relaxed.sys.global.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "l"(p), "l"(cmp), "l"(val) : "memory");
+    else asm volatile("atom.relaxed.gpu.global.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "l"(p), "l"(cmp), "l"(val) : "memory");
     return old;
 }
 template <bool SYS> __device__ __forceinline__ void red_add_s32(int* p, int v) {
