@@ -761,7 +761,11 @@ def run_extras(args, st, out):
     fns = {"all_resident": extra_all_resident, "distribution": extra_distribution, "backends": extra_backends, "stress": extra_stress}
     for n in names:
         t0 = time.time()
-        extras[n] = fns[n](args, st)
+        try:
+            extras[n] = fns[n](args, st)
+        except Exception as e:  # an extra must never cost the main line (every rank takes the same path: same inputs)
+            import traceback
+            extras[n] = {"error": "%s: %s" % (type(e).__name__, e), "where": traceback.format_exc().strip().splitlines()[-3:]}
         if isinstance(extras[n], dict):
             extras[n]["seconds"] = round(time.time() - t0, 1)
         if out is not None:
@@ -838,6 +842,9 @@ def main():
         timer.start()
         try:
             run_extras(args, state, out_box[0])
+        except Exception as e:
+            if out_box[0] is not None:
+                out_box[0].setdefault("extras", {})["error"] = "%s: %s" % (type(e).__name__, e)
         finally:
             timer.cancel()
         if comm.global_rank == 0:

@@ -41,7 +41,8 @@ def eviction_storm(comm, device, launches, rows=4096, sets=2, check_every=1, tag
         S = cache.num_sets()
         ids = np.arange(ds.num_nodes, dtype=np.int64)
         pool = ids[((ids // G) % S) < sets]  # partitioned hashing: owner id % G, set (id / G) % S (M/cache_kernel.cu:11, M/nvshmem_cache.h:193-196)
-        assert len(pool) > 32 * sets * G * 2, "pool must overflow the sets it maps to"
+        # ids per (owner, set) = N / (G * S): 156 at G = 2, 39 at G = 8 on the `tiny` table - always more than the 32 ways
+        assert len(pool) > 32 * sets * G, "pool must overflow the sets it maps to"
         rng = np.random.default_rng(100 + comm.global_rank)
         n_lists = 64
         lists = [torch.from_numpy(pool[rng.integers(0, len(pool), rows)]).to(device) for _ in range(n_lists)]
