@@ -104,6 +104,18 @@ class ClockSampler(object):
                 "samples": len(sm), "samples_whole_run": len(self.rows)}
 
 
+def workload_string(args, ds, D, L):
+    """One description of the measured workload, identical in both arms (the driver compares the two lines' config)."""
+    return ("%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), SAGE fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
+            % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, args.batch_size, args.cache_size, args.cache_backend, D, L, args.distribution))
+
+
+def domains_for(args):
+    """(D, L) of a run with --gpus N and --gpus_per_domain (0 = one domain spanning the box), as MPI_Comm_Manager lays them out."""
+    L = args.gpus_per_domain if args.gpus_per_domain else args.gpus
+    return max(1, args.gpus // max(1, L)), L
+
+
 def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads=None):
     """The reference's CPU formulation of the path (BASELINE.json: "DGL CPU sampler + torch index_select gather"):
     the oracle's OpenMP restatement of the DGL CPU sampler + to_block (DGL is absent from the image), then
@@ -569,8 +581,9 @@ def run_ours(args, state):
                  main_res=res, main_loader=loader, main_pipe=pipe)
     if comm.global_rank == 0:
         # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this same workload
-        # (profiles/r1b_gather_full_raw.csv: 77.1 MB + 88.9 MB); only quoted for the configuration it was captured on
-        traffic = 166.0e6 if (N == 1 and args.shape == "igb-medium" and args.cache_size == 16384 and args.fan_out == "5,5" and B == 1024) else None
+        # (profiles/r2_gather_n1_bench_full_raw.csv: 78.8 MB + 89.0 MB; pcie__read_bytes 39.7 MB for 36.0 MB of missed rows);
+        # only quoted for the configuration it was captured on
+        traffic = 167.8e6 if (N == 1 and args.shape == "igb-medium" and args.cache_size == 16384 and args.fan_out == "5,5" and B == 1024) else None
         t_meas = res["gather_kernel_ms"] * 1e-3
 
         def replay_block(r):
@@ -581,8 +594,7 @@ def run_ours(args, state):
             "metric": METRIC, "value": res["value"], "unit": "mini-batches/s", "n_gpus": N, "steps": K, "warmup": args.warmup,
             "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "ours",
-            "config": {"workload": "%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), SAGE fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
-                       % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, B, args.cache_size, args.cache_backend, comm.num_master_process, L, args.distribution),
+            "config": {"workload": workload_string(args, ds, comm.num_master_process, L),
                        "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (a different row set every step; the table is %.0f GB, L2 is 126 MB)" % (res["rows_per_step"] * R / 1e6, ds.num_nodes * R / 1e9),
                        "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter,
                        "colour_metadata": ds.color_source,
@@ -796,8 +808,9 @@ def main():
             line = {"metric": METRIC, "value": r["batches_per_s"], "unit": "mini-batches/s", "n_gpus": args.gpus, "steps": args.steps,
                     "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                     "dtype": "f32", "data": "synthetic", "impl": "reference",
-                    "config": {"workload": "%s, SAGE fan-out %s, batch %d: CPU sampler (OpenMP restatement of the DGL CPU sampler, DGL absent) + torch.index_select gather on %d host threads"
-                               % (args.shape, args.fan_out, args.batch_size, r["threads"])},
+                    "config": {"workload": workload_string(args, ds, *domains_for(args)),
+                               "arm": "the reference's CPU formulation of the same workload: CPU sampler (OpenMP restatement of the DGL CPU sampler, DGL absent) + "
+                                      "torch.index_select gather on %d host threads; the cache / backend / distribution fields of `workload` name the GPU arm's setting" % r["threads"]},
                     "cpu_baseline": {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
                                      "sample": "%d mini-batches of %d seeds (%.0f gathered rows each)" % (r["steps"], args.batch_size, r["rows_per_step"])},
                     "gather_GBs": r["gather_GBs"],

@@ -83,7 +83,8 @@ class SyntheticSharedCSCUVA(object):
                              "graph_gpu": "Graph_Coloring GPU mode on this graph (level-synchronous variant of the reference's colouring, same seeds)"}[self._color_mode(n)]
         self.color_file, self.topk_file, self.score_file = (os.path.join(self.meta_dir, x) for x in ("color.npy", "topk.npy", "score.npy"))
         if verbose and comm_manager.global_rank == 0:
-            print("dataset %s ready in %.1fs (features %.1fs)" % (shape, time.time() - t0, t_feat), flush=True)
+            import sys
+            sys.stderr.write("dataset %s ready in %.1fs (features %.1fs)\n" % (shape, time.time() - t0, t_feat))
 
     @staticmethod
     def _color_mode(n):
