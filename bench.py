@@ -60,7 +60,9 @@ def parse_args():
     p.add_argument("--extras", default=os.environ.get("COALA_BENCH_EXTRAS", "auto"),
                    help="auto | none | comma list of all_resident,distribution,backends,stress")
     p.add_argument("--extras_budget", type=float, default=300.0, help="seconds after which the extras are abandoned and the main line printed")
-    p.add_argument("--hbm_indptr", action="store_true", help="B200 option: sampler keeps a copy of indptr (80 MB) in HBM")
+    p.add_argument("--hbm_indptr", type=int, default=None, choices=[0, 1], help="sampler keeps a copy of indptr (80 MB at igb-medium) in HBM "
+                   "(default: COALA_HBM_INDPTR, which defaults to 1)")
+    p.add_argument("--hbm_graph", action="store_true", help="B200 option: the neighbour lists (indices, 0.96 GB at igb-medium) in HBM as well")
     p.add_argument("--no_prefetch", action="store_true", help="diagnostic: sample and gather of a batch back to back, no batch in flight")
     p.add_argument("--profile_e2e", action="store_true", help="cProfile the host side of the e2e loop (rank 0) to stderr")
     p.add_argument("--cuda_profiler_range", action="store_true",
@@ -226,7 +228,8 @@ def build_world(args, comm=None, ds=None, cache_size=None, backend=None, distrib
     train = torch.from_numpy(synth.train_ids(ds.num_nodes, seed=0))
     nd = Node_Distributor(comm, train, args.batch_size, ds.color_file, ds.topk_file, ds.score_file,
                           parsing_method=distribution or args.distribution)
-    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank, hbm_indptr=True if args.hbm_indptr else None)
+    sampler = MultiLayerNeighborSampler(fan, seed=1, rank=comm.global_rank, hbm_indptr=None if args.hbm_indptr is None else bool(args.hbm_indptr),
+                                        hbm_graph=True if args.hbm_graph else None)
     loader = COALA_GNN_DataLoader(SSD_INFO(1, ds.cache_dim * 4, 1024, 0), nd, ds.graph, sampler, args.batch_size, ds.dim, fan,
                                   cache_size or args.cache_size, device, refresh_counter=args.refresh_counter,
                                   cache_backend=backend or args.cache_backend, sim_buf=ds.feat_data)
@@ -598,7 +601,8 @@ def run_ours(args, state):
                        "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (a different row set every step; the table is %.0f GB, L2 is 126 MB)" % (res["rows_per_step"] * R / 1e6, ds.num_nodes * R / 1e9),
                        "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter,
                        "colour_metadata": ds.color_source,
-                       "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr copy in HBM" if sampler.hbm_indptr else "")},
+                       "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr and indices copies in HBM" if sampler.hbm_graph else
+                                                                                            ", indptr copy in HBM" if sampler.hbm_indptr else "")},
             "timing": {"protocol": "barrier+synchronize, %d untimed refill steps, then %d back-to-back windows of %d steps (one CUDA event per window on the consumer stream, "
                                    "no drain in between), barrier+synchronize; max over ranks per window; value = median window" % (pipe.engine.depth, res["windows"], K),
                        "windows": res["windows"], "window_ms_min_med_max": res["window_ms_min_med_max"], "mean_value_all_windows": res["mean_value_all_windows"],

@@ -69,6 +69,8 @@ SIGNATURES = {
     "coala_sampler_destroy": (None, [_vp]),
     "coala_sampler_max_sample": (_i64, [_vp]),
     "coala_sampler_stage_indptr": (_i32, [_vp]),
+    "coala_sampler_stage_indices": (_i32, [_vp]),
+    "coala_sampler_share_indptr": (_i32, [_vp, _vp]),
     "coala_sampler_trace": (_i32, [_vp, _vp, _i32]),
     "coala_sampler_graph_nodes": (_i32, [_vp]),
     "coala_sampler_sample_async": (_i32, [_vp, _u64, _i32, _u64, _vp]),

@@ -383,7 +383,9 @@ struct coala_sampler {
     int64_t* h_counts = nullptr;       // pinned mirror of ctl->counts
     cudaEvent_t done = nullptr;
     int sm_count = 148;
-    int64_t* indptr_hbm = nullptr;     // optional HBM copy of indptr (coala_sampler_stage_indptr)
+    int64_t* indptr_hbm = nullptr;     // HBM copy of indptr (coala_sampler_stage_indptr), or another sampler's (coala_sampler_share_indptr)
+    int64_t* indices_hbm = nullptr;    // HBM copy of indices (coala_sampler_stage_indices), same sharing rule
+    bool indptr_owned = false, indices_owned = false;
     uint64_t seq = 0;                  // samples enqueued so far (drives the table versions)
     // the whole sample as one CUDA graph: one launch instead of 7 (every launch is a command fetch over
     // the same host link the path keeps busy); only the first node's arguments are patched per batch
@@ -491,7 +493,9 @@ extern "C" void coala_sampler_destroy(coala_sampler* s) {
         cudaFree(s->e_src[l]); cudaFree(s->e_dst[l]); cudaFree(s->e_id[l]); cudaFree(s->e_src_local[l]);
         cudaFree(s->val[l]); cudaFree(s->rank[l]);
     }
-    cudaFree(s->indptr_hbm); cudaFree(s->ctl); cudaFree(s->status_rows); cudaFree(s->status_edges);
+    if (s->indptr_owned) cudaFree(s->indptr_hbm);
+    if (s->indices_owned) cudaFree(s->indices_hbm);
+    cudaFree(s->ctl); cudaFree(s->status_rows); cudaFree(s->status_edges);
     if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
     if (s->graph) cudaGraphDestroy(s->graph);
     if (s->cap_stream) cudaStreamDestroy(s->cap_stream);
@@ -506,14 +510,46 @@ extern "C" void coala_sampler_destroy(coala_sampler* s) {
 
 extern "C" int64_t coala_sampler_max_sample(coala_sampler* s) { return s->ns_max[s->L]; }
 
+static void drop_graph(coala_sampler* s) {  // the captured graph holds the old CSC addresses
+    if (s->graph_exec) { cudaGraphExecDestroy(s->graph_exec); s->graph_exec = nullptr; }
+    if (s->graph) { cudaGraphDestroy(s->graph); s->graph = nullptr; }
+}
 extern "C" int coala_sampler_stage_indptr(coala_sampler* s) {
     if (s->indptr_hbm) return 0;
     COALA_CUDA(cudaSetDevice(s->device));
     COALA_CUDA(cudaMalloc(&s->indptr_hbm, (size_t)(s->num_nodes + 1) * 8));
     COALA_CUDA(cudaMemcpy(s->indptr_hbm, s->indptr, (size_t)(s->num_nodes + 1) * 8, cudaMemcpyDefault));
     s->indptr = s->indptr_hbm;
-    if (s->graph_exec) { cudaGraphExecDestroy(s->graph_exec); s->graph_exec = nullptr; }
-    if (s->graph) { cudaGraphDestroy(s->graph); s->graph = nullptr; }
+    s->indptr_owned = true;
+    drop_graph(s);
+    return 0;
+}
+// B200 option: the neighbour lists too (8 bytes per edge: 0.96 GB at igb-medium, 12.9 GB at papers100M, 32 GB at IGB-full, all
+// small beside 180 GB).  With both arrays staged a sample never leaves the device.
+extern "C" int coala_sampler_stage_indices(coala_sampler* s) {
+    if (s->indices_hbm) return 0;
+    COALA_CUDA(cudaSetDevice(s->device));
+    int64_t nnz = 0;
+    COALA_CUDA(cudaMemcpy(&nnz, s->indptr + s->num_nodes, 8, cudaMemcpyDefault));
+    if (nnz < 0) COALA_FAIL("stage_indices: indptr[num_nodes] is negative");
+    COALA_CUDA(cudaMalloc(&s->indices_hbm, (size_t)std::max<int64_t>(nnz, 1) * 8));
+    COALA_CUDA(cudaMemcpy(s->indices_hbm, s->indices, (size_t)nnz * 8, cudaMemcpyDefault));
+    s->indices = s->indices_hbm;
+    s->indices_owned = true;
+    drop_graph(s);
+    return 0;
+}
+// The samplers of one engine walk the same graph: one staged copy serves all of them.  `from` must outlive `s`.
+extern "C" int coala_sampler_share_indptr(coala_sampler* s, const coala_sampler* from) {
+    if (!from->indptr_hbm || from->num_nodes != s->num_nodes || from->device != s->device || s->indptr_hbm || s->indices_hbm)
+        COALA_FAIL("share_indptr: the other sampler has no staged indptr for this graph and device");
+    s->indptr_hbm = from->indptr_hbm;
+    s->indptr = s->indptr_hbm;
+    if (from->indices_hbm) {
+        s->indices_hbm = from->indices_hbm;
+        s->indices = s->indices_hbm;
+    }
+    drop_graph(s);
     return 0;
 }
 extern "C" uint64_t coala_sampler_input_count_dev_ptr(coala_sampler* s) { return (uint64_t)(&s->ctl->counts[s->L]); }

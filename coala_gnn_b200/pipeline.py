@@ -28,9 +28,9 @@ from .sampler import MultiLayerNeighborSampler, batch_key  # noqa: F401  (batch_
 class _Slot(object):
     """Python face of one native engine slot: its sampler object, output rows, stream and seed staging buffer."""
 
-    def __init__(self, k, fanouts, graph, batch_size, out, device, hbm_indptr=None):
+    def __init__(self, k, fanouts, graph, batch_size, out, device, hbm_indptr=None, indptr_from=None, hbm_graph=None):
         self.k = k
-        self.sampler = MultiLayerNeighborSampler(fanouts, hbm_indptr=hbm_indptr)
+        self.sampler = MultiLayerNeighborSampler(fanouts, hbm_indptr=hbm_indptr, indptr_from=indptr_from, hbm_graph=hbm_graph)
         self.sampler._ensure(graph, batch_size)
         self.sampler._last_g = graph
         self.out = out
@@ -71,7 +71,10 @@ class BatchEngine(object):
         self._h = check_handle(self._lib.coala_engine_create(dev_index, self.nslots, self.batch_size, self._seed & ((1 << 64) - 1), self.rank,
                                                              1 if record_gather_events else 0), "engine")
         outs = manager.out_buffers(self.nslots)
-        self.slots = [_Slot(k, self.fanouts, graph, batch_size, outs[k], device, getattr(sampler, "hbm_indptr", None)) for k in range(self.nslots)]
+        self.slots = []
+        for k in range(self.nslots):  # slot 0 stages indptr in HBM (unless switched off), the others use its copy
+            self.slots.append(_Slot(k, self.fanouts, graph, batch_size, outs[k], device, getattr(sampler, "hbm_indptr", None),
+                                    self.slots[0].sampler if k else None, getattr(sampler, "hbm_graph", None)))
         for s in self.slots:
             check(self._lib.coala_engine_bind_slot(self._h, s.k, s.sampler._h, s.out.data_ptr()), "engine slot")
             s.stream = torch.cuda.ExternalStream(int(self._lib.coala_engine_slot_stream(self._h, s.k)), device=device)

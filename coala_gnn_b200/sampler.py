@@ -167,9 +167,18 @@ class MultiLayerNeighborSampler:
     """Uniform in-neighbour sampling without replacement, one round per fan-out in reverse order,
     each followed by to_block. `seed` fixes the RNG stream; the k-th call uses batch_key(seed, k, rank)."""
 
-    def __init__(self, fanouts, seed=0, rank=0, hbm_indptr=None):
+    def __init__(self, fanouts, seed=0, rank=0, hbm_indptr=None, indptr_from=None, hbm_graph=None):
         import os
-        self.hbm_indptr = bool(int(os.environ.get("COALA_HBM_INDPTR", "0"))) if hbm_indptr is None else bool(hbm_indptr)
+        # indptr (8 (N + 1) bytes) is copied to HBM unless COALA_HBM_INDPTR=0 / hbm_indptr=False: the two dependent host reads of
+        # every sampled row become one (+12 % mini-batches/s where the pipeline is not host-link bound; BASELINE.md 4.5).
+        # `indptr_from`: another sampler of the same graph and device whose copy this one uses (the slots of one engine).
+        self.hbm_indptr = bool(int(os.environ.get("COALA_HBM_INDPTR", "1"))) if hbm_indptr is None else bool(hbm_indptr)
+        # COALA_HBM_GRAPH=1 / hbm_graph=True: the neighbour lists (8 bytes per edge) are copied as well - opt-in, because every rank
+        # of a node then holds its own copy of what the reference shares once in host memory.
+        self.hbm_graph = bool(int(os.environ.get("COALA_HBM_GRAPH", "0"))) if hbm_graph is None else bool(hbm_graph)
+        if self.hbm_graph:
+            self.hbm_indptr = True
+        self._indptr_from = indptr_from
         self.fanouts = [int(f) for f in fanouts]
         self.seed, self.rank, self.calls = int(seed), int(rank), 0
         self._h, self._graph_id, self._max_seeds = None, None, 0
@@ -190,7 +199,14 @@ class MultiLayerNeighborSampler:
         self._h = check_handle(lib().coala_sampler_create(dev_index, g.indptr.data_ptr(), g.indices.data_ptr(), eptr,
                                                           g.number_of_nodes(), int(n_seeds), fan, len(self.fanouts)), "sampler")
         if self.hbm_indptr:
-            check(lib().coala_sampler_stage_indptr(self._h), "stage indptr")
+            src = self._indptr_from
+            if src is not None and src._h is not None and src._graph_id == key and src.hbm_indptr and src.hbm_graph == self.hbm_graph:
+                check(lib().coala_sampler_share_indptr(self._h, src._h), "share indptr")
+            else:
+                self._indptr_from = None
+                check(lib().coala_sampler_stage_indptr(self._h), "stage indptr")
+                if self.hbm_graph:
+                    check(lib().coala_sampler_stage_indices(self._h), "stage indices")
         self._graph_id, self._max_seeds = key, int(n_seeds)
         self._device = "cuda:%d" % dev_index
 

@@ -185,10 +185,15 @@ coala_sampler* coala_sampler_create(int device, uint64_t indptr_ptr, uint64_t in
                                     int64_t num_nodes, int max_seeds, const int* fanouts, int n_layers);
 void coala_sampler_destroy(coala_sampler* s);
 int64_t coala_sampler_max_sample(coala_sampler* s);
-/* B200 option (off by default): keep a private copy of indptr (8(N+1) bytes: 80 MB at 10 M nodes) in
- * HBM, which removes the first of the two dependent host round trips of every sampled row.  indices
- * and edge ids stay in pinned host memory. */
+/* B200 layout: keep a copy of indptr (8(N+1) bytes: 80 MB at 10 M nodes) in HBM, which removes the
+ * first of the two dependent host round trips of every sampled row (the Python layer does this unless
+ * COALA_HBM_INDPTR=0).  stage_indices copies the neighbour lists too (8 bytes per edge; opt-in,
+ * COALA_HBM_GRAPH=1): a sample then never leaves the device.  Edge ids stay in pinned host memory
+ * (they are looked up on demand). */
 int coala_sampler_stage_indptr(coala_sampler* s);
+int coala_sampler_stage_indices(coala_sampler* s);
+/* use the copies another sampler of the same graph and device staged (that sampler must be destroyed last) */
+int coala_sampler_share_indptr(coala_sampler* s, const coala_sampler* from);
 /* diagnostics (COALA_SAMPLER_TRACE=1 at creation): average milliseconds between consecutive enqueued
  * operations of a sample (per round: sample_rows, first_occurrence, relabel; finally the count read-back).
  * Returns the number of intervals written. */

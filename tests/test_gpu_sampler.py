@@ -54,6 +54,34 @@ def test_sampled_blocks_bit_exact_vs_oracle(fanouts, pinned):
         _compare(blocks, eblocks)
 
 
+@pytest.mark.parametrize("indptr_at", ["host", "hbm", "hbm_shared", "graph", "graph_shared"])
+def test_graph_placement_does_not_change_the_sample(indptr_at):
+    """indptr read through UVA, from the sampler's HBM copy (the default), or from another sampler's copy (the slots of one
+    engine share slot 0's); with `graph` the neighbour lists are staged as well (COALA_HBM_GRAPH=1): same blocks, bit for bit."""
+    import torch
+    from coala_gnn_b200.sampler import MultiLayerNeighborSampler
+    indptr, indices, eids = synth.make_csc(20000, 240000, 9)
+    g = _uva_graph(indptr, indices, eids, True)
+    whole = indptr_at.startswith("graph")
+    owner = MultiLayerNeighborSampler([10, 5], seed=4, rank=1, hbm_indptr=True, hbm_graph=whole)
+    owner._ensure(g, 256)
+    sampler = {"host": lambda: MultiLayerNeighborSampler([10, 5], seed=4, rank=1, hbm_indptr=False),
+               "hbm": lambda: MultiLayerNeighborSampler([10, 5], seed=4, rank=1),
+               "hbm_shared": lambda: MultiLayerNeighborSampler([10, 5], seed=4, rank=1, indptr_from=owner),
+               "graph": lambda: MultiLayerNeighborSampler([10, 5], seed=4, rank=1, hbm_graph=True),
+               "graph_shared": lambda: MultiLayerNeighborSampler([10, 5], seed=4, rank=1, hbm_graph=True, indptr_from=owner)}[indptr_at]()
+    assert sampler.hbm_indptr == (indptr_at != "host") and sampler.hbm_graph == whole
+    items = synth.train_ids(20000, seed=5)
+    for it in range(2):
+        seeds = items[it * 256:(it + 1) * 256]
+        inp, outn, blocks = sampler.sample(g, torch.from_numpy(seeds).cuda())
+        einp, eout, eblocks = oracle.sample_blocks_detailed(indptr, indices, eids, seeds, [10, 5], oracle.batch_key(4, it, 1))
+        assert np.array_equal(inp.cpu().numpy(), einp) and np.array_equal(outn.cpu().numpy(), eout)
+        _compare(blocks, eblocks)
+    assert (sampler._indptr_from is owner) == indptr_at.endswith("_shared")
+    del sampler, owner
+
+
 def test_full_fanout_is_exact_csc_and_edge_ids_optional():
     """A graph whose maximum in-degree is <= the fan-out: every row keeps all in-edges in CSC order."""
     import torch
