@@ -10,6 +10,8 @@
 //   slot stream k (high priority): [wait consumer, wait previous gather of the slot] seeds H2D -> sample (one CUDA graph)
 //   gather stream                : [wait sample, wait consumer] cached gather of the sampler's input-node list
 // depth+1 slots rotate; events order slot reuse exactly as pipeline.BatchEngine did.
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "common.cuh"
@@ -57,12 +59,16 @@ extern "C" coala_engine* coala_engine_create(int device, int n_slots, int batch_
     e->device = device; e->n_slots = n_slots; e->batch_size = batch_size; e->seed = seed; e->rank = rank; e->record = record_times != 0;
     int lo = 0, hi = 0;
     COALA_CUDA_NULL(cudaDeviceGetStreamPriorityRange(&lo, &hi));
-    COALA_CUDA_NULL(cudaStreamCreateWithFlags(&e->s_gather, cudaStreamNonBlocking));
+    // COALA_ENGINE_PRIORITY: which side gets the high stream priority - "sample" (default), "gather" or "none"
+    const char* pr = getenv("COALA_ENGINE_PRIORITY");
+    const int pr_sample = (pr && (!strcmp(pr, "gather") || !strcmp(pr, "none"))) ? lo : hi;
+    const int pr_gather = (pr && !strcmp(pr, "gather")) ? hi : lo;
+    COALA_CUDA_NULL(cudaStreamCreateWithPriority(&e->s_gather, cudaStreamNonBlocking, pr_gather));
     COALA_CUDA_NULL(cudaEventCreateWithFlags(&e->ev_consumed, cudaEventDisableTiming));
     e->slots.resize(n_slots);
     for (auto& s : e->slots) {
         // sampling kernels are small and latency bound: high priority so that they take SM slots as gather CTAs retire
-        COALA_CUDA_NULL(cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, hi));
+        COALA_CUDA_NULL(cudaStreamCreateWithPriority(&s.stream, cudaStreamNonBlocking, pr_sample));
         COALA_CUDA_NULL(cudaEventCreateWithFlags(&s.ev_sampled, cudaEventDisableTiming));
         COALA_CUDA_NULL(cudaEventCreateWithFlags(&s.ev_gathered, cudaEventDisableTiming));
         if (e->record) {

@@ -15,6 +15,8 @@ S="python bench.py --shape igb-small --cache_size 4096 --steps 20 --warmup 5 --p
 timeout 200 $S > gpurun_out/r2_16_small_default.json 2> gpurun_out/r2_16_small_default.err; show gpurun_out/r2_16_small_default.json small_default
 timeout 200 $S --hbm_indptr 0 > gpurun_out/r2_16_small_uva.json 2> gpurun_out/r2_16_small_uva.err; show gpurun_out/r2_16_small_uva.json small_uva
 timeout 200 $S --hbm_graph > gpurun_out/r2_16_small_graph.json 2> gpurun_out/r2_16_small_graph.err; show gpurun_out/r2_16_small_graph.json small_graph
+COALA_ENGINE_PRIORITY=gather timeout 200 $S > gpurun_out/r2_16_small_prio_gather.json 2> gpurun_out/r2_16_small_prio_gather.err; show gpurun_out/r2_16_small_prio_gather.json small_prio_gather
+COALA_ENGINE_PRIORITY=none timeout 200 $S > gpurun_out/r2_16_small_prio_none.json 2> gpurun_out/r2_16_small_prio_none.err; show gpurun_out/r2_16_small_prio_none.json small_prio_none
 M="python bench.py --gpus 1 --steps 20 --warmup 5 --no_cpu_baseline --extras none"
 timeout 600 $M > gpurun_out/r2_16_n1_default.json 2> gpurun_out/r2_16_n1_default.err; show gpurun_out/r2_16_n1_default.json n1_default
 timeout 600 $M --hbm_graph > gpurun_out/r2_16_n1_graph.json 2> gpurun_out/r2_16_n1_graph.err; show gpurun_out/r2_16_n1_graph.json n1_graph
