@@ -115,6 +115,7 @@ SIGNATURES = {
     "coala_probe_read_bandwidth": (_i32, [_u64, _i64, _i32, _vp]),
     "coala_enable_peer_access": (_i32, [_i32, _i32]),
     "coala_probe_gather": (_i32, [_u64, _u64, _u64, _i64, _i32, _i32, _i32, _i32, _vp]),
+    "coala_probe_gather_all": (_i32, [_i32, _vp, _vp, _vp, _i64, _i32, _i32, _i32, _vp]),
     "coala_probe_random_read": (_i32, [_u64, _i64, _i32, _i32, _i32, _i32, _vp]),
 }
 

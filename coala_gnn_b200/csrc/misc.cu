@@ -312,3 +312,81 @@ extern "C" int coala_probe_random_read(uint64_t src_ptr, int64_t bytes, int span
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(sink);
     return 0;
 }
+
+// The same probe with the table hash-partitioned over G GPUs of this process like the cache (owner = id % G, row = id / G) and
+// ALL G GPUs gathering at once: the practical ceiling of the N-GPU all-hit regime, where every GPU pulls (G-1)/G of its rows
+// over NVLink while serving its peers.  Launches are issued iteration-major so the devices stay in step.
+struct ProbeTables { const uint4* t[8]; int G; };
+
+template <int VPL, int RIF>
+__global__ void probe_gather_all_kernel(const __grid_constant__ ProbeTables pt, const int64_t* __restrict__ idx, uint4* __restrict__ out, int64_t n) {
+    const unsigned lane = threadIdx.x & 31;
+    const int64_t warps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+    int64_t w = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    constexpr int RV = VPL * 32;
+    const uint64_t G = (uint64_t)pt.G;
+    for (int64_t r = w * RIF; r < n; r += warps * RIF) {
+        uint4 v[RIF][VPL];
+#pragma unroll
+        for (int j = 0; j < RIF; j++) {
+            if (r + j < n) {
+                const uint64_t id = (uint64_t)__ldg(idx + r + j);
+                const uint4* src = pt.t[id % G] + (id / G) * RV;
+#pragma unroll
+                for (int k = 0; k < VPL; k++) v[j][k] = ld_host_v4(src + k * 32 + lane);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < RIF; j++) {
+            if (r + j < n) {
+                uint4* dst = out + (uint64_t)(r + j) * RV;
+#pragma unroll
+                for (int k = 0; k < VPL; k++) st_out_v4(dst + k * 32 + lane, v[j][k]);
+            }
+        }
+    }
+}
+
+// tables[g] = device g's part (peer access between all pairs must be enabled), idx[g] / out[g] = device g's id list
+// (iters * n ids) and output rows; us_per_launch[g] = device g's mean launch time while all G run.  4 KB rows only.
+extern "C" int coala_probe_gather_all(int G, const uint64_t* tables, const uint64_t* idx, const uint64_t* out, int64_t n, int rows_in_flight,
+                                      int ctas_per_sm, int iters, double* us_per_launch) {
+    if (G < 1 || G > 8) COALA_FAIL("probe_gather_all: 1..8 GPUs");
+    if (rows_in_flight != 1 && rows_in_flight != 2) COALA_FAIL("probe_gather_all: rows_in_flight 1 or 2");
+    ProbeTables pt;
+    pt.G = G;
+    for (int g = 0; g < 8; g++) pt.t[g] = reinterpret_cast<const uint4*>(tables[g < G ? g : 0]);
+    int sms = 148;
+    COALA_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
+    const unsigned grid = (unsigned)(sms * (ctas_per_sm < 1 ? 1 : ctas_per_sm));
+    cudaEvent_t e0[8], e1[8];
+    for (int g = 0; g < G; g++) {
+        COALA_CUDA(cudaSetDevice(g));
+        COALA_CUDA(cudaEventCreate(&e0[g]));
+        COALA_CUDA(cudaEventCreate(&e1[g]));
+    }
+    auto go = [&](int g, int it) {
+        const int64_t* p = reinterpret_cast<const int64_t*>(idx[g]) + (int64_t)it * n;
+        uint4* o = reinterpret_cast<uint4*>(out[g]);
+        if (rows_in_flight == 2) probe_gather_all_kernel<8, 2><<<grid, 256>>>(pt, p, o, n);
+        else probe_gather_all_kernel<8, 1><<<grid, 256>>>(pt, p, o, n);
+    };
+    for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); go(g, 0); }
+    for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); COALA_CUDA(cudaDeviceSynchronize()); }
+    for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); COALA_CUDA(cudaEventRecord(e0[g])); }
+    for (int i = 0; i < iters; i++)
+        for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); go(g, iters > 1 ? i : 0); }
+    for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); COALA_CUDA(cudaEventRecord(e1[g])); }
+    for (int g = 0; g < G; g++) {
+        COALA_CUDA(cudaSetDevice(g));
+        COALA_CUDA(cudaEventSynchronize(e1[g]));
+        COALA_CUDA(cudaGetLastError());
+        float ms = 0;
+        COALA_CUDA(cudaEventElapsedTime(&ms, e0[g], e1[g]));
+        us_per_launch[g] = 1e3 * ms / iters;
+        cudaEventDestroy(e0[g]); cudaEventDestroy(e1[g]);
+    }
+    COALA_CUDA(cudaSetDevice(0));
+    return 0;
+}
+

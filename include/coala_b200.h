@@ -298,6 +298,11 @@ int coala_enable_peer_access(int device, int peer);
  * launch); rows_in_flight 1|2 per warp; ctas_per_sm CTAs of 256 threads per SM; returns the mean launch time (CUDA events). */
 int coala_probe_gather(uint64_t table_ptr, uint64_t idx_ptr, uint64_t out_ptr, int64_t n, int row_bytes, int rows_in_flight,
                        int ctas_per_sm, int iters, double* us_per_launch);
+/* the same with the table hash-partitioned over the G GPUs of this process like the cache (owner id % G, row id / G; 4 KB rows)
+ * and all G GPUs gathering at once: tables[g] / idx[g] / out[g] are device g's part, id lists (iters * n) and output rows;
+ * peer access must be enabled between all pairs; us_per_launch[g] = device g's mean launch time while all run. */
+int coala_probe_gather_all(int G, const uint64_t* tables, const uint64_t* idx, const uint64_t* out, int64_t n, int rows_in_flight,
+                           int ctas_per_sm, int iters, double* us_per_launch);
 
 /* random-read probe: independent locations per second when each location is read as `span_bytes`
  * (8/32/64/128/256) contiguous bytes by neighbouring lanes; misalign != 0 starts 96 B into a 256-B granule */
