@@ -26,15 +26,18 @@ struct MetaPtrs {
     const int32_t* p[ND_MAX_DOMAINS];
 };
 
-// scores[i*D + j] = sum_k meta_j[topk[c,k]] * score[c,k]   (M/node_distributor_pybind.cuh:172-203)
+// scores[j*N + i] = sum_k meta_j[topk[c,k]] * score[c,k]   (M/node_distributor_pybind.cuh:172-203)
+// Domain-major: consecutive threads of the assign kernel (consecutive seeds) then read consecutive doubles.  With the
+// seed-major layout every warp load touched 32 lines and one tile step cost 4 us at D = 8, 10 us at D = 16
+// (profiles/r2_launches_distributor_config_shapes.csv: 56 / 290 us per call).
 __global__ void nd_score_kernel(const int64_t* __restrict__ items, int64_t N, int D, int K,
                                 const int32_t* __restrict__ color, const int32_t* __restrict__ topk,
                                 const double* __restrict__ score, MetaPtrs meta, int meta_len,
                                 double* __restrict__ scores, int* __restrict__ neg_flag) {
     int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= N * D) return;
-    int64_t i = t / D;
-    int j = (int)(t % D);
+    int64_t i = t % N;
+    int j = (int)(t / N);
     int64_t id = items[i];
     int c = color[id];
     double s = 0.0;
@@ -76,7 +79,7 @@ __global__ void __launch_bounds__(ND_TILE) nd_assign_kernel(const int64_t* __res
             int best = 0;
             double best_score = -1.0;
             for (int j = 0; j < D; j++) {
-                double s = scores[i * D + j];
+                double s = scores[(int64_t)j * N + i];
                 if (run[j] == cap) s = -1.0;                 // (:205-206)
                 if (s > best_score) { best = j; best_score = s; }  // (:208-211)
             }
@@ -128,7 +131,7 @@ __global__ void nd_assign_serial_kernel(const int64_t* __restrict__ items, int64
         int best = 0;
         double best_score = -1.0;
         for (int j = 0; j < D; j++) {
-            double s = scores[i * D + j];
+            double s = scores[(int64_t)j * N + i];
             if (len[j] == cap) s = -1.0;
             if (s > best_score) { best = j; best_score = s; }
         }
