@@ -58,6 +58,8 @@ SIGNATURES = {
     "coala_cache_export_state": (_i32, [_vp, _vp, _vp, _vp]),
     "coala_cache_set_copy_engine": (_i32, [_vp, _i32]),
     "coala_split_node_list": (_i32, [_u64, _i64, _u64, _u64, _u64, _i32, _i32, _vp]),
+    "coala_split_node_list_static": (_i32, [_u64, _i64, _u64, _u64, _u64, _i32, _i32, _vp]),
+    "coala_split_node_list_static_max_ids": (_i64, []),
     "coala_map_feat_data": (_i32, [_u64, _u64, _u64, _i64, _i32, _vp]),
     "coala_nccl_unique_id": (_i32, [_vp]),
     "coala_nccl_version": (_i32, []),

@@ -106,6 +106,78 @@ extern "C" int coala_split_node_list(uint64_t idx_ptr, int64_t n, uint64_t node_
     return 0;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// coala_split_node_list_static: the same stable partition for callers that are not allowed to allocate.
+//
+// Who that is: code that drives this library from inside somebody else's memory budget - a host that has handed the
+// whole GPU to one pool allocator (a framework's caching allocator, an RMM pool, a MIG slice sized to the byte) and
+// forbids any side allocation from a plugin, or a real-time / inference loop in which cudaMalloc / cudaMallocAsync are
+// banned because they may take driver locks, grow a pool or synchronise the device at an unpredictable moment.
+// coala_split_node_list above needs nblocks * G ints between its three kernels and gets them from cudaMallocAsync;
+// this variant keeps that scratch in the library image instead.
+//
+// The scratch is the file-scope array below: STATIC_MAX_BLOCKS * COALA_MAX_GPUS ints = 128 KiB, which every GPU that
+// loads this library carries until the process exits.  It bounds one call at COALA_SPLIT_STATIC_MAX_IDS
+// (2 097 152) ids - above the largest request list any configuration in BASELINE.json produces (1 362 944).
+//
+// `g_part_static_scratch` as written in host code is only the host-side shadow of the symbol, not something a kernel can
+// dereference, so the device address is looked up with cudaGetSymbolAddress - once per device, with that device
+// current - and cached in s_static_scratch[dev].  That look-up happens in the FIRST call on each device (it may load
+// the module on that device), so make that first call during set-up, outside any stream capture.
+//
+// Every call on a device uses the same array and the array keeps whatever the previous call left in it.  Nothing has
+// to start at zero: part_count_kernel writes all nblocks * G words before part_scan_kernel / part_scatter_kernel read
+// them, so left-over contents are never observed.  What the sharing does forbid is overlap: two calls whose kernels
+// can be on the GPU at the same time (different streams, or two host threads) race on the array and corrupt each
+// other's buckets - keep calls on one device stream-ordered one after the other.
+namespace {
+constexpr int STATIC_MAX_BLOCKS = 2048;                          // * PT ids per call
+constexpr int64_t STATIC_MAX_IDS = (int64_t)STATIC_MAX_BLOCKS * PT;  // 2 097 152
+constexpr int STATIC_MAX_DEVICES = 64;
+static __device__ __align__(256) int g_part_static_scratch[STATIC_MAX_BLOCKS * COALA_MAX_GPUS];
+std::mutex s_static_mu;
+int* s_static_scratch[STATIC_MAX_DEVICES] = {};  // device address of the array on device d, nullptr = not looked up yet
+
+// device address of g_part_static_scratch on the current device (set-up on first use; no allocation)
+int static_scratch_for_current_device(int** out) {
+    int dev = -1;
+    COALA_CUDA(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= STATIC_MAX_DEVICES) COALA_FAIL("split_node_list_static: device ordinal out of range");
+    std::lock_guard<std::mutex> lk(s_static_mu);
+    if (!s_static_scratch[dev]) {
+        int* p = nullptr;
+        COALA_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_part_static_scratch));
+        if (!p) COALA_FAIL("split_node_list_static: cudaGetSymbolAddress returned a null address");
+        s_static_scratch[dev] = p;
+    }
+    *out = s_static_scratch[dev];
+    return 0;
+}
+}  // namespace
+
+extern "C" int64_t coala_split_node_list_static_max_ids(void) { return STATIC_MAX_IDS; }
+
+extern "C" int coala_split_node_list_static(uint64_t idx_ptr, int64_t n, uint64_t node_ptr, uint64_t map_ptr, uint64_t counter_ptr,
+                                            int n_gpus, int max_sample, void* stream) {
+    if (n_gpus < 1 || n_gpus > COALA_MAX_GPUS) COALA_FAIL("split_node_list_static: n_gpus out of range");
+    if (n > STATIC_MAX_IDS)
+        COALA_FAIL("split_node_list_static: n = " + std::to_string(n) + " ids exceeds the built-in scratch (at most " +
+                   std::to_string(STATIC_MAX_IDS) + " ids per call); use coala_split_node_list or split the list");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int64_t* counter = reinterpret_cast<int64_t*>(counter_ptr);
+    int* block_cnt = nullptr;
+    if (static_scratch_for_current_device(&block_cnt) != 0) return -1;  // also on the n <= 0 path: set-up is call-count independent
+    if (n <= 0) { COALA_CUDA(cudaMemsetAsync(counter, 0, n_gpus * 8, st)); return 0; }
+    const int nblocks = (int)((n + PT - 1) / PT);
+    const int64_t* idx = reinterpret_cast<const int64_t*>(idx_ptr);
+    part_count_kernel<<<nblocks, PT, 0, st>>>(idx, n, nullptr, n_gpus, block_cnt);
+    part_scan_kernel<<<1, 32, 0, st>>>(block_cnt, nblocks, n_gpus, counter, 1);
+    part_scatter_kernel<<<nblocks, PT, 0, st>>>(idx, n, nullptr, n_gpus, max_sample, max_sample, block_cnt, reinterpret_cast<int64_t*>(node_ptr),
+                                                reinterpret_cast<int64_t*>(map_ptr));
+    COALA_CUDA(cudaGetLastError());
+    return 0;
+}
+
 // internal form used by the NCCL exchange (nccl_backend.cu): row count on the device, bucket g = [count | ids...] at
 // buckets + g * (1 + max_sample), caller-owned scratch (no allocation on the hot path)
 int coala_partition_buckets(const int64_t* idx, int64_t n_upper, const int64_t* n_dev, int64_t* buckets, int64_t* map, int n_gpus,

@@ -155,6 +155,24 @@ int coala_cache_set_copy_engine(coala_cache* c, int engine);
  * partition by id % n_gpus: node[max_sample*g + k], map[...] = original position, counter[g]. */
 int coala_split_node_list(uint64_t idx_ptr, int64_t n, uint64_t node_ptr, uint64_t map_ptr, uint64_t counter_ptr,
                           int n_gpus, int max_sample, void* stream);
+/* No counterpart in the reference (its split_node_list, cited above, has no allocation-free form).
+ * coala_split_node_list_static is coala_split_node_list - same arguments, same buckets, bit for bit - for callers that
+ * may not allocate device memory: plugins living inside a host whose GPU memory belongs to one pool allocator (a
+ * framework's caching allocator, an RMM pool, a MIG slice budgeted to the byte), and latency-critical loops where
+ * cudaMalloc / cudaMallocAsync are banned because they can take driver locks or synchronise the device.  The
+ * nblocks x n_gpus block-count scratch the three kernels share lives in a 128 KiB static __device__ array inside the
+ * library (held by every GPU that loads it, until exit) instead of coming from cudaMallocAsync; the call performs no
+ * cudaMalloc / cudaFree / pool operation of any kind.
+ *   limit      n <= coala_split_node_list_static_max_ids() = 2 097 152 ids per call; larger n fails with a message
+ *              (nothing is launched) - use coala_split_node_list, or split the list.
+ *   set-up     the first call on each device (with that device current, as for every call here) resolves the
+ *              array's device address with cudaGetSymbolAddress; make that call before any stream capture.
+ *   sharing    all calls on a device use the one array, which keeps the previous call's contents.  No word is read
+ *              before this call has written it, so nothing needs clearing - but two calls whose kernels can overlap on
+ *              the GPU (different streams / threads) race on it.  Keep them stream-ordered. */
+int coala_split_node_list_static(uint64_t idx_ptr, int64_t n, uint64_t node_ptr, uint64_t map_ptr, uint64_t counter_ptr,
+                                 int n_gpus, int max_sample, void* stream);
+int64_t coala_split_node_list_static_max_ids(void);
 /* map_feat_data (M/ssd_gnn_cache.cuh:327-356, M/cache_kernel.cu:113-137): out[map[r]] = src[r] */
 int coala_map_feat_data(uint64_t out_ptr, uint64_t src_ptr, uint64_t map_ptr, int64_t n, int feat_dim, void* stream);
 
