@@ -33,7 +33,12 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
-METRIC = "mini-batches/s (IGB-medium-shaped synthetic graph, SAGE fan-out 5,5, batch 1024 per GPU; seed distribution + UVA sampling + cached feature gather)"
+def metric_string(args):
+    """BASELINE.json's metric, worded for the shape / fan-out / batch actually run (a papers100m 10,10,10 run is not labelled IGB-medium 5,5)."""
+    return ("mini-batches/s (%s-shaped synthetic graph, %d-layer neighbour sampling fan-out %s, batch %d per GPU; seed distribution + UVA sampling + cached feature gather)"
+            % (args.shape, len(args.fan_out.split(",")), args.fan_out, args.batch_size))
+
+
 NVL_PEAK = 770.0  # GB/s per direction: the measured peer-copy figure of B200_PROFILING.md (900 nominal); scripts/bench_gather.py reads 777 with a kernel
 
 
@@ -108,8 +113,8 @@ class ClockSampler(object):
 
 def workload_string(args, ds, D, L):
     """One description of the measured workload, identical in both arms (the driver compares the two lines' config)."""
-    return ("%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), SAGE fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
-            % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, args.fan_out, args.batch_size, args.cache_size, args.cache_backend, D, L, args.distribution))
+    return ("%s (%d nodes, %d edges, %d-d fp32 features pinned in host memory), %d-layer fan-out %s, batch %d/GPU, %d MB cache/GPU, backend %s (%dx%d domain), distribution %s"
+            % (args.shape, ds.num_nodes, ds.num_edges, ds.dim, len(args.fan_out.split(",")), args.fan_out, args.batch_size, args.cache_size, args.cache_backend, D, L, args.distribution))
 
 
 def domains_for(args):
@@ -118,7 +123,7 @@ def domains_for(args):
     return max(1, args.gpus // max(1, L)), L
 
 
-def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads=None):
+def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads=None, first=0):
     """The reference's CPU formulation of the path (BASELINE.json: "DGL CPU sampler + torch index_select gather"):
     the oracle's OpenMP restatement of the DGL CPU sampler + to_block (DGL is absent from the image), then
     torch.index_select on the host feature table with all host threads."""
@@ -136,9 +141,9 @@ def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads
     i = 0
     t_end = time.time() + seconds if seconds else None
     while True:
-        seeds = train[(i % (len(train) // B - 1)) * B:][:B]
+        seeds = train[((first + i) % (len(train) // B - 1)) * B:][:B]
         t0 = time.perf_counter()
-        inp, _ = oracle.sample_blocks_fast(indptr, indices, seeds, fan, oracle.batch_key(1, i), max_sample, threads)
+        inp, _ = oracle.sample_blocks_fast(indptr, indices, seeds, fan, oracle.batch_key(1, first + i), max_sample, threads)
         torch.index_select(feat_t, 0, torch.from_numpy(inp), out=out[:len(inp)])
         dt = time.perf_counter() - t0
         if i >= warmup:
@@ -152,6 +157,31 @@ def cpu_path(ds_host, train, B, fan, seconds=None, steps=None, warmup=2, threads
     tot = float(np.sum(times))
     return {"batches_per_s": len(times) / tot, "ms_per_step": 1e3 * tot / len(times), "rows_per_step": rows / len(times),
             "gather_GBs": rows * feat.shape[1] * 4 / tot / 1e9, "steps": len(times), "threads": threads}
+
+
+def cpu_path_windows(ds_host, train, B, fan, steps, warmup, min_seconds, settle_seconds=10.0, threads=None):
+    """The CPU arm under the GPU arm's protocol: warm up until the rate has settled (two consecutive windows within 5 %, at
+    least `warmup` batches, at most `settle_seconds`: the first seconds run 25-30 % slow while the OpenMP team, torch's
+    thread pool and the page tables of the 41 GB table warm up), then windows of `steps` batches until they cover
+    `min_seconds`; value = median window."""
+    w = cpu_path(ds_host, train, B, fan, steps=max(steps, warmup), warmup=0, threads=threads)
+    t_end, n_warm, prev = time.time() + settle_seconds, w["steps"], w["batches_per_s"]
+    while time.time() < t_end:
+        w = cpu_path(ds_host, train, B, fan, steps=steps, warmup=0, threads=threads, first=n_warm)
+        n_warm += w["steps"]
+        settled = abs(w["batches_per_s"] - prev) <= 0.05 * prev
+        prev = w["batches_per_s"]
+        if settled:
+            break
+    wins, covered = [], 0.0
+    while covered < min_seconds or len(wins) < 3:
+        w = cpu_path(ds_host, train, B, fan, steps=steps, warmup=0, threads=threads, first=n_warm + len(wins) * steps)
+        wins.append(w)
+        covered += w["steps"] / w["batches_per_s"]
+    wins.sort(key=lambda x: x["batches_per_s"])
+    med = dict(wins[len(wins) // 2])
+    med.update(windows=len(wins), warm_batches=n_warm, window_rate_min_med_max=[wins[0]["batches_per_s"], med["batches_per_s"], wins[-1]["batches_per_s"]])
+    return med
 
 
 # ------------------------------------------------------------------------------------------------------------
@@ -594,13 +624,15 @@ def run_ours(args, state):
                     "hbm": {"achieved": 2.0 * R * n_last / (r["ms"] * 1e-3) / 1e9, "peak": hbm_peak, "frac": 2.0 * R * n_last / (r["ms"] * 1e-3) / 1e9 / hbm_peak},
                     "nvlink_in": {"achieved": R * n_last * remote / (r["ms"] * 1e-3) / 1e9, "peak": NVL_PEAK, "frac": R * n_last * remote / (r["ms"] * 1e-3) / 1e9 / NVL_PEAK}}
         out = {
-            "metric": METRIC, "value": res["value"], "unit": "mini-batches/s", "n_gpus": N, "steps": K, "warmup": args.warmup,
+            "metric": metric_string(args), "value": res["value"], "unit": "mini-batches/s", "n_gpus": N, "steps": K, "warmup": args.warmup,
             "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
             "data": "synthetic", "impl": "ours",
             "config": {"workload": workload_string(args, ds, comm.num_master_process, L),
                        "l2": "each step gathers ~%.0f MB of rows chosen by fresh sampling (a different row set every step; the table is %.0f GB, L2 is 126 MB)" % (res["rows_per_step"] * R / 1e6, ds.num_nodes * R / 1e9),
                        "cache_prewarm_batches": n_pre, "refresh_counter": args.refresh_counter,
                        "colour_metadata": ds.color_source,
+                       "cache_protocol": "read-back ordered writers (COALA_CACHE_FENCED=0, validated on B200 only)" if os.environ.get("COALA_CACHE_FENCED", "1") == "0"
+                                         else "fenced writers (PTX acquire / fence.acq_rel, default)",
                        "graph": "CSC indptr/indices/edge_ids in pinned host memory (UVA)" + (", indptr and indices copies in HBM" if sampler.hbm_graph else
                                                                                             ", indptr copy in HBM" if sampler.hbm_indptr else "")},
             "timing": {"protocol": "barrier+synchronize, %d untimed refill steps, then %d back-to-back windows of %d steps (one CUDA event per window on the consumer stream, "
@@ -618,7 +650,10 @@ def run_ours(args, state):
             # the dominant kernel against the link that bounds it (T_bound = max over links of bytes/peak);
             # `hbm` is always listed too, and `all_hit_replay` times the same kernel on resident rows (the HBM / NVLink regime)
             "roofline": {"bound": binding, "achieved": links[binding]["achieved"], "peak": links[binding]["peak"], "unit": "GB/s",
-                         "frac": links[binding]["frac"], "traffic": traffic, "peak_source": links[binding]["peak_source"],
+                         "frac": links[binding]["frac"], "traffic": traffic,
+                         "traffic_source": ("profiles/r2_gather_n1_bench_full_raw.csv (ncu --set full of this workload, dram__bytes_read.sum + dram__bytes_write.sum per launch; "
+                                            "not re-measured in this run)") if traffic else None,
+                         "peak_source": links[binding]["peak_source"],
                          "kernel": "coala_gather_kernel", "kernel_ms": res["gather_kernel_ms"], "kernel_share_of_step": res["gather_kernel_ms"] / res["ms_per_step"],
                          "links": links,
                          "all_hit_replay": dict(rows=n_last, **{k: replay_block(v) for k, v in replay.items() if k.startswith("engine_")})},
@@ -788,6 +823,63 @@ def run_extras(args, st, out):
             out["extras"] = extras  # visible to the watchdog as soon as a section is complete
 
 
+def finalize_parity(out):
+    """Make the line self-verifying.  The driver keeps `e2e`, `roofline` and `config` whole but only the NAMES of other keys,
+    so a compact parity summary is copied into the first two and the headline extras into `config`; a main-line parity
+    failure voids the number (`value`: null) and the process exits non-zero.  Returns the exit code."""
+    par = out.get("parity", {})
+    legs = [par.get("value_leg", {}), par.get("e2e_leg", {})]
+    ok = bool(par) and par.get("mismatches", 1) == 0 and all(l.get("ok", False) for l in legs)
+    extras = out.get("extras", {}) or {}
+
+    def walk(d, path, bad):  # every nested block that carries an `ok` flag next to parity-style counters
+        if isinstance(d, dict):
+            if "ok" in d and ("mismatches" in d or "corrupt_rows" in d) and not d["ok"]:
+                bad.append(path)
+            for k, v in d.items():
+                walk(v, path + "." + str(k), bad)
+    bad = []
+    walk(extras, "extras", bad)
+    stress = extras.get("stress", {}) if isinstance(extras.get("stress"), dict) else {}
+    summary = {"parity_ok": ok, "parity_rows_checked": par.get("rows_checked"), "parity_ranks": par.get("ranks"),
+               "seed_lists_checked": sum(l.get("seed_lists_checked", 0) for l in legs),
+               "blocks_checked": sum(l.get("blocks_checked", 0) for l in legs),
+               "stress_corrupt_rows": stress.get("corrupt_rows"), "extras_parity_ok": not bad}
+    out["e2e"].update(summary)
+    out["roofline"].update(summary)
+    out["extras_parity_ok"] = not bad
+    if bad:
+        out["extras_parity_failed"] = bad
+
+    def pick(d, *keys):
+        for k in keys:
+            d = d.get(k) if isinstance(d, dict) else None
+        return round(d, 4) if isinstance(d, float) else d
+    head = {"all_resident.value": pick(extras, "all_resident", "value"),
+            "all_resident.binding_link_frac": pick(extras, "all_resident", "binding_link_frac")}
+    dist = extras.get("distribution")
+    if isinstance(dist, dict):
+        for shape, row in (dist.get("layouts") or {}).items():
+            if isinstance(row, dict):
+                for m in ("baseline", "node_color"):
+                    if isinstance(row.get(m), dict):
+                        head["distribution.%s.%s.hit_ratio" % (shape, m)] = pick(row, m, "hit_ratio")
+                        head["distribution.%s.%s.value" % (shape, m)] = pick(row, m, "value")
+    back = extras.get("backends")
+    if isinstance(back, dict):
+        for b in ("p2p", "isolated", "nccl"):
+            if isinstance(back.get(b), dict):
+                head["backends.%s.value" % b] = pick(back, b, "value")
+    out["config"]["extras_summary"] = {k: v for k, v in head.items() if v is not None}
+    if not ok:
+        out["value_voided_by_parity"] = out.get("value")
+        out["value"] = None
+        out["e2e"]["value_voided_by_parity"] = out["e2e"].get("value")
+        out["e2e"]["value"] = None
+        return 3
+    return 0
+
+
 def main():
     args = parse_args()
     if os.environ.get("COALA_HANG_DUMP"):  # debugging aid: dump every thread's stack if the run stalls
@@ -808,15 +900,19 @@ def main():
         try:
             fan = [int(f) for f in args.fan_out.split(",")]
             train = synth.train_ids(ds.num_nodes, seed=0)
-            r = cpu_path((ds.csc_host[0], ds.csc_host[1], ds.feat_host_array()), train, args.batch_size, fan, steps=args.steps, warmup=args.warmup)
-            line = {"metric": METRIC, "value": r["batches_per_s"], "unit": "mini-batches/s", "n_gpus": args.gpus, "steps": args.steps,
+            r = cpu_path_windows((ds.csc_host[0], ds.csc_host[1], ds.feat_host_array()), train, args.batch_size, fan, args.steps, args.warmup,
+                                 args.min_seconds)
+            line = {"metric": metric_string(args), "value": r["batches_per_s"], "unit": "mini-batches/s", "n_gpus": args.gpus, "steps": args.steps,
                     "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                     "dtype": "f32", "data": "synthetic", "impl": "reference",
                     "config": {"workload": workload_string(args, ds, *domains_for(args)),
                                "arm": "the reference's CPU formulation of the same workload: CPU sampler (OpenMP restatement of the DGL CPU sampler, DGL absent) + "
                                       "torch.index_select gather on %d host threads; the cache / backend / distribution fields of `workload` name the GPU arm's setting" % r["threads"]},
                     "cpu_baseline": {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
-                                     "sample": "%d mini-batches of %d seeds (%.0f gathered rows each)" % (r["steps"], args.batch_size, r["rows_per_step"])},
+                                     "sample": "median of %d windows of %d mini-batches of %d seeds (%.0f gathered rows each) after %d warm-up batches; window rates min/med/max %.0f/%.0f/%.0f"
+                                               % (r["windows"], r["steps"], args.batch_size, r["rows_per_step"], r["warm_batches"], *r["window_rate_min_med_max"])},
+                    "timing": {"protocol": "warm-up until two consecutive windows agree within 5 % (<= 10 s), then windows of --steps batches for >= --min_seconds; value = median window",
+                               "windows": r["windows"], "warm_batches": r["warm_batches"]},
                     "gather_GBs": r["gather_GBs"],
                     "e2e": {"value": r["batches_per_s"], "unit": "mini-batches/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
             print(json.dumps(line), flush=True)
@@ -832,6 +928,8 @@ def main():
     printed = threading.Event()
     out_box = [None]
 
+    exit_code = [0]
+
     def emit(note=None):
         if printed.is_set():
             return
@@ -839,6 +937,8 @@ def main():
         if out_box[0] is not None:
             if note:
                 out_box[0].setdefault("extras", {})["abandoned"] = note
+            if "roofline" in out_box[0]:  # rank 0's line
+                exit_code[0] = finalize_parity(out_box[0])
             print(json.dumps(out_box[0]), flush=True)
 
     def bail():  # the extras must never cost the main line: print what is complete and leave (every rank has the same timer)
@@ -848,7 +948,7 @@ def main():
             if ds is not None:
                 ds.unlink_segments()  # kernels may still be reading the mappings: drop the names only
         finally:
-            os._exit(0)
+            os._exit(exit_code[0])
 
     comm = None
     try:
@@ -867,11 +967,13 @@ def main():
         if comm.global_rank == 0:
             ds, train, fan = state["ds"], state["train"], state["fan"]
             if world == 1 and not args.no_cpu_baseline:
-                r = cpu_path((ds.csc_host[0], ds.csc_host[1], ds.feat_host_array()), train.numpy(), args.batch_size, fan,
-                             seconds=args.cpu_baseline_seconds)
+                # the same protocol as `--impl reference` (settle, then windows of --steps, median), so the two CPU numbers of one box agree
+                r = cpu_path_windows((ds.csc_host[0], ds.csc_host[1], ds.feat_host_array()), train.numpy(), args.batch_size, fan, args.steps, args.warmup,
+                                     args.cpu_baseline_seconds)
                 out_box[0]["cpu_baseline"] = {"value": r["batches_per_s"], "unit": "mini-batches/s", "cores": r["threads"], "kind": "port",
-                                              "sample": "%d mini-batches of %d seeds in %.1f s (oracle OpenMP sampler + torch.index_select, %.1f GB/s gathered)"
-                                                        % (r["steps"], args.batch_size, r["steps"] / r["batches_per_s"], r["gather_GBs"])}
+                                              "sample": "median of %d windows of %d mini-batches of %d seeds after %d warm-up batches (oracle OpenMP sampler + torch.index_select, "
+                                                        "%.1f GB/s gathered); window rates min/med/max %.0f/%.0f/%.0f"
+                                                        % (r["windows"], r["steps"], args.batch_size, r["warm_batches"], r["gather_GBs"], *r["window_rate_min_med_max"])}
             emit()
     finally:
         comm = state.get("comm")
@@ -890,7 +992,7 @@ def main():
                 dist.destroy_process_group()
             except Exception:
                 pass
-    return 0
+    return exit_code[0]
 
 
 if __name__ == "__main__":

@@ -2,6 +2,7 @@
 // Replaces the host classes of M/ssd_gnn_cache.cuh and the handle ctors of
 // M/isolated_cache.h:519-636 / M/nvshmem_cache.h:524-641.
 #include "cache.cuh"
+#include <atomic>
 #include "distributor.h"
 #include "vmm.h"
 #include <unistd.h>
@@ -46,6 +47,8 @@ void coala_set_error(const std::string& msg) { g_last_error = msg; }
 extern "C" const char* coala_last_error(void) { return g_last_error.c_str(); }
 extern "C" int coala_abi_version(void) { return 1; }
 
+constexpr int GATHER_WORK_POOL = 8;  // launches of one cache object that may be in flight at once (any streams)
+
 struct coala_cache {
     int kind, device, feat_dim, cache_dim, global_rank, local_rank, n_gpus, num_colors;
     uint64_t num_sets;
@@ -63,8 +66,13 @@ struct coala_cache {
     int ctas_per_sm = 2;   // resident CTAs per SM of the gather's single wave (see launch_gather)
     size_t smem_per_sm = 228 * 1024;
     int sm_count = 148;
-    GatherWork* d_work = nullptr;  // rotating pool of device-side work counters (one per in-flight launch)
-    unsigned launch_seq = 0;
+    GatherWork* d_work = nullptr;  // pool of device-side work counters: an entry belongs to one launch until that launch has finished
+    GatherWork* cur_work = nullptr;                 // entry of the launch being enqueued (valid under work_mu)
+    cudaEvent_t work_ev[GATHER_WORK_POOL] = {};     // recorded behind the launch that last used entry k
+    bool work_armed[GATHER_WORK_POOL] = {};         // work_ev[k] has been recorded at least once
+    unsigned launch_seq = 0;                        // next entry to try (under work_mu)
+    uint64_t color_len = 0;                         // entries of the distributor's colour table (0: none): upper bound of id_limit
+    std::mutex work_mu;                             // launches of one cache object may come from several host threads
     std::vector<int32_t> h_counters;
 };
 
@@ -77,9 +85,38 @@ extern "C" int coala_cache_dim_for(int dim) {
     return -1;  // "Only Feature Embedding Size less than 8KB is supported" (M/ssd_gnn_cache.cuh:43-44)
 }
 
-constexpr int GATHER_WORK_POOL = 8;  // launches of one cache object that may be in flight at once (different streams)
+static GatherWork* next_work(coala_cache* c) { return c->cur_work; }
 
-static GatherWork* next_work(coala_cache* c) { return c->d_work + (c->launch_seq++ % GATHER_WORK_POOL); }
+// Choose the pool entry of the launch about to be enqueued on `st` (caller holds work_mu).  The kernel's last CTA re-arms
+// the entry, so an entry may only be handed out again once the launch that used it has COMPLETED - not merely once eight
+// later launches were enqueued: a launch still queued on one stream while another stream starts a later one on the same
+// entry would share `next` / `done` with it (chunks skipped, output rows never written).  Each entry therefore carries an
+// event recorded right behind its launch; an entry is reused when that event has completed, and when every entry is in
+// flight the host waits for the oldest.  While `st` is being captured, events cannot be queried: captured launches rotate
+// through the pool as before and must not overlap other launches of the same cache object.
+static int acquire_work(coala_cache* c, cudaStream_t st, int* slot, bool* record) {
+    cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+    COALA_CUDA(cudaStreamIsCapturing(st, &cs));
+    if (cs != cudaStreamCaptureStatusNone) {
+        *slot = (int)(c->launch_seq++ % GATHER_WORK_POOL);
+        *record = false;
+        return 0;
+    }
+    *record = true;
+    for (int k = 0; k < GATHER_WORK_POOL; k++) {
+        const int i = (int)((c->launch_seq + k) % GATHER_WORK_POOL);
+        if (!c->work_armed[i]) { *slot = i; c->launch_seq = i + 1; return 0; }
+        const cudaError_t q = cudaEventQuery(c->work_ev[i]);
+        if (q == cudaSuccess) { *slot = i; c->launch_seq = i + 1; return 0; }
+        if (q != cudaErrorNotReady) COALA_CUDA(q);
+        (void)cudaGetLastError();  // "not ready" is an answer, not a failure: keep it out of the launch's error check
+    }
+    const int i = (int)(c->launch_seq % GATHER_WORK_POOL);  // the oldest
+    COALA_CUDA(cudaEventSynchronize(c->work_ev[i]));
+    *slot = i;
+    c->launch_seq = i + 1;
+    return 0;
+}
 
 // One resident wave: `ctas_per_sm` CTAs of 8 warps per SM pull chunks of rows from a device-side counter (cache.cuh) until
 // the list - whose length may only be known on the device - is exhausted.
@@ -101,8 +138,13 @@ static int launch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t
         // big enough that resident+1 CTAs cannot fit, small enough to leave >= 16 KB per SM for the
         // (1 KB each) driver reservations of the other streams' CTAs
         const size_t smem = (size_t)(c->smem_per_sm / resident) - 16384;
-        // per device, and cheap: set on every launch rather than tracking (device, instantiation) pairs
-        COALA_CUDA(cudaFuncSetAttribute(coala_gather_kernel<VPL, SYS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        // the attribute is per (device, instantiation): set it when the value changes, not on every launch
+        static std::atomic<int> smem_set[64];
+        const bool track = c->device >= 0 && c->device < 64;
+        if (!track || smem_set[c->device].load(std::memory_order_relaxed) != (int)smem) {
+            COALA_CUDA(cudaFuncSetAttribute(coala_gather_kernel<VPL, SYS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            if (track) smem_set[c->device].store((int)smem, std::memory_order_relaxed);
+        }
         int64_t blocks = (int64_t)c->sm_count * resident;
         const int64_t need = (n + (int64_t)wpb * GATHER_CH - 1) / ((int64_t)wpb * GATHER_CH);
         if (blocks > need) blocks = need;
@@ -121,7 +163,12 @@ static int launch_gather_bulk(coala_cache* c, const int64_t* idx, float* out, in
     const size_t need_smem = (size_t)wpb * NBUF * c->row_bytes;
     size_t smem = (size_t)(c->smem_per_sm / resident) - 16384;
     if (smem < need_smem) smem = need_smem;
-    COALA_CUDA(cudaFuncSetAttribute(coala_gather_bulk_kernel<VPL, SYS, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    static std::atomic<int> smem_set[64];
+    const bool track = c->device >= 0 && c->device < 64;
+    if (!track || smem_set[c->device].load(std::memory_order_relaxed) != (int)smem) {
+        COALA_CUDA(cudaFuncSetAttribute(coala_gather_bulk_kernel<VPL, SYS, NBUF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        if (track) smem_set[c->device].store((int)smem, std::memory_order_relaxed);
+    }
     int64_t blocks = (int64_t)c->sm_count * resident;
     const int64_t need = (n + (int64_t)wpb * GATHER_CH - 1) / ((int64_t)wpb * GATHER_CH);
     if (blocks > need) blocks = need;
@@ -130,8 +177,27 @@ static int launch_gather_bulk(coala_cache* c, const int64_t* idx, float* out, in
     return 0;
 }
 
+static int dispatch_gather_locked(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
+                                  bool serial);
+
 static int dispatch_gather(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
                            bool serial) {
+    if (n <= 0) return 0;
+    std::lock_guard<std::mutex> lk(c->work_mu);
+    int slot = 0;
+    bool record = false;
+    if (acquire_work(c, st, &slot, &record) != 0) return -1;
+    c->cur_work = c->d_work + slot;
+    if (dispatch_gather_locked(c, idx, out, n, n_dev, st, serial) != 0) return -1;
+    if (record) {
+        COALA_CUDA(cudaEventRecord(c->work_ev[slot], st));
+        c->work_armed[slot] = true;
+    }
+    return 0;
+}
+
+static int dispatch_gather_locked(coala_cache* c, const int64_t* idx, float* out, int64_t n, const int64_t* n_dev, cudaStream_t st,
+                                  bool serial) {
     const bool sys = c->kind == COALA_CACHE_PARTITIONED && c->n_gpus > 1;
     const int vpl = c->row_bytes / 512;
     // bulk copies need 16-byte aligned output rows of a 16-byte multiple
@@ -216,6 +282,7 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     COALA_CUDA_NULL(cudaMemset(c->d_stats, 0, 4 * sizeof(unsigned long long)));
     COALA_CUDA_NULL(cudaMalloc(&c->d_work, GATHER_WORK_POOL * sizeof(GatherWork)));
     COALA_CUDA_NULL(cudaMemset(c->d_work, 0, GATHER_WORK_POOL * sizeof(GatherWork)));
+    for (int k = 0; k < GATHER_WORK_POOL; k++) COALA_CUDA_NULL(cudaEventCreateWithFlags(&c->work_ev[k], cudaEventDisableTiming));
 
     CacheParams& p = c->params;
     memset(&p, 0, sizeof(p));
@@ -231,14 +298,14 @@ extern "C" coala_cache* coala_cache_create(int kind, int device, int feat_dim, c
     p.out_stride = feat_dim;
     p.out_dim = feat_dim < cache_dim ? feat_dim : cache_dim;
     p.stats = c->d_stats;
-    p.fenced = 0;
+    p.fenced = 1;  // PTX-model-exact writer protocol; COALA_CACHE_FENCED=0 opts into the read-back-ordered one (cache.cuh)
     if (const char* e = getenv("COALA_CACHE_FENCED")) p.fenced = atoi(e) != 0;
     p.zero = 0;
     // ids are bounds-checked on the device: against the tag's id field always, against the table's row count as
     // soon as it is known (from the distributor's colour table, or coala_cache_set_num_nodes)
     p.id_limit = TAG_ID_MASK;
     if (nd && coala_nd_num_graph_nodes(nd) > 0 && (uint64_t)coala_nd_num_graph_nodes(nd) < p.id_limit)
-        p.id_limit = (uint64_t)coala_nd_num_graph_nodes(nd);
+        p.id_limit = c->color_len = (uint64_t)coala_nd_num_graph_nodes(nd);
     if (const char* e = getenv("COALA_GATHER_CTAS_PER_SM")) c->ctas_per_sm = atoi(e) >= 1 && atoi(e) <= 3 ? atoi(e) : 2;
     if (const char* e = getenv("COALA_GATHER_ENGINE")) c->copy_engine = atoi(e) == 1 ? 1 : 0;
     if (const char* e = getenv("COALA_GATHER_NBUF")) c->bulk_nbuf = atoi(e) == 2 ? 2 : 3;
@@ -263,6 +330,8 @@ extern "C" void coala_cache_destroy(coala_cache* c) {
     else if (c->slab) cudaFree(c->slab);
     if (c->d_stats) cudaFree(c->d_stats);
     if (c->d_work) cudaFree(c->d_work);
+    for (int k = 0; k < GATHER_WORK_POOL; k++)
+        if (c->work_ev[k]) cudaEventDestroy(c->work_ev[k]);
     delete c;
 }
 
@@ -372,7 +441,9 @@ static int fail_on_refused_ids(coala_cache* c, const char* what) {
 
 extern "C" int coala_cache_set_num_nodes(coala_cache* c, int64_t num_nodes) {
     if (num_nodes <= 0) COALA_FAIL("set_num_nodes: the host table has at least one row");
-    c->params.id_limit = (uint64_t)num_nodes < TAG_ID_MASK ? (uint64_t)num_nodes : TAG_ID_MASK;
+    uint64_t lim = (uint64_t)num_nodes < TAG_ID_MASK ? (uint64_t)num_nodes : TAG_ID_MASK;
+    if (c->color_len && lim > c->color_len) lim = c->color_len;  // the fill path indexes the colour table with the id as well
+    c->params.id_limit = lim;
     return 0;
 }
 

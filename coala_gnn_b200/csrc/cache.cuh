@@ -51,7 +51,7 @@ struct CacheParams {
     unsigned long long* stats;  // [0]=hit [1]=miss [2]=bypass [3]=ids refused (>= id_limit)
     uint64_t id_limit;       // ids >= id_limit are refused: min(rows of the host table, 2^40 - 1 = the tag's id field)
     uint32_t zero;           // always 0 at run time; unknown to the compiler (see read_line_validated)
-    int fenced;              // 1: writers order their stores with fence.acq_rel (PTX-model-exact); 0: by read-back + dependency
+    int fenced;              // 1 (default): writers order their stores with fence.acq_rel (PTX-model-exact); 0: by read-back + dependency
 };
 
 constexpr int LOCK_TRIES = 64;     // CAS attempts on a set lock before bypassing
@@ -168,14 +168,18 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
 
     // Writer-side ordering.  The protocol needs three orders: (a) the lock is taken before the set is re-probed, (b) the
     // busy tag is in place before the unlock and before any line word changes, (c) every line word is in place before the
-    // tag turns even again.  With p.fenced they are PTX acquire / release / fence.acq_rel (MEMBAR.{GPU,SYS}).  Measured on
-    // B200 a system-scope MEMBAR in this kernel completes in ~20 us (it waits for every access the thread has in flight,
-    // the host-row loads over PCIe included): three per fill put the launch's critical path into a handful of late
-    // misses (profiles/r2_gather_miss03_before.txt: 8 % of all warp time in MEMBAR, 27 % idle at the final barrier behind
-    // it).  Default (p.fenced == 0): the same orders by READ-BACK + register dependency, like the reader side - all of
-    // these are strong accesses that resolve at the owner's L2, the single coherence point of the shard: a strong load of
-    // the word just stored returns only once that store is performed there (same-address order), and an access whose
-    // address depends on the returned value is issued after it.  Two round trips to the owner's L2 per fill, no MEMBAR.
+    // tag turns even again.
+    //   p.fenced != 0 (DEFAULT since round 3): PTX acquire on the lock CAS and the re-probe, one fence.acq_rel for (b), one
+    //   for (c) - two MEMBAR.{GPU,SYS} per fill (round 2 had three; the release store of the unlock was redundant next to
+    //   the fence).  A MEMBAR waits for every access the thread has in flight, the host-row loads over PCIe included.  At
+    //   GPU scope (one GPU per cache domain) this costs nothing measurable; at system scope (shards of peers) it costs
+    //   19 % on a 3 %-miss launch and 23 % of the N = 2 pipeline (profiles/r3_fenced_vs_readback.txt).
+    //   p.fenced == 0 (COALA_CACHE_FENCED=0): the same orders by READ-BACK + register dependency, like the reader side -
+    //   all of these are strong accesses that resolve at the owner's L2, the single coherence point of the shard: a strong
+    //   load of the word just stored returns only once that store is performed there (same-address order), and an access
+    //   whose address depends on the returned value is issued after it.  Two round trips to the owner's L2 per fill, no
+    //   MEMBAR.  The PTX memory model does not promise dependency ordering of relaxed accesses: this mode is validated
+    //   empirically on B200 only (storm tests), which is why it is opt-in.
     const bool fenced = p.fenced != 0;
     uint64_t s = 0;
     bool locked = false;
@@ -257,8 +261,10 @@ __device__ __forceinline__ int resolve_row(const CacheParams& p, uint64_t id, in
             red_add_s32<SYS>(sh.color_counters + newc, 1);
         }
         if (fenced) {
-            st_release_u64<SYS>(sh.set_seq + set, s + 2);  // unlock; the line stays busy via its tag
-            fence_acq_rel<SYS>();                            // busy tag visible before any line data
+            // ONE fence covers both orders of (b): the busy tag (and colour word) precede the unlock - fence + relaxed
+            // store is a release pattern - and, through the __syncwarp below, every lane's line stores
+            fence_acq_rel<SYS>();
+            st_relaxed_u64<SYS>(sh.set_seq + set, s + 2);  // unlock; the line stays busy via its tag
         } else {
             // (b): the busy tag is read back from the owner's L2; the unlock and (through `dep`) every line store depend on it
             // (the colour word of the slot is read back with it: the slot's next filler reads it under the lock)

@@ -1,6 +1,7 @@
 // Shared helpers for the sm_100a kernels of the COALA-GNN data path.
 #pragma once
 #include <cuda_runtime.h>
+#include <atomic>
 #include <cstdint>
 #include <cstdio>
 #include <cstdlib>
@@ -34,6 +35,19 @@ void coala_set_error(const std::string& msg);
             return nullptr;                                                                    \
         }                                                                                      \
     } while (0)
+
+// SM count of the current device, looked up once per device: grid caps are written as multiples of it
+inline int coala_sm_count() {
+    static std::atomic<int> cached[64];
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    int v = cached[dev].load(std::memory_order_relaxed);
+    if (v <= 0) {
+        if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+        cached[dev].store(v, std::memory_order_relaxed);
+    }
+    return v;
+}
 
 #define COALA_FAIL(msg)          \
     do {                         \

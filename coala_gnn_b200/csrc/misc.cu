@@ -97,7 +97,7 @@ extern "C" int coala_synth_fill_features(uint64_t dst_ptr, uint64_t seed, int64_
                                          int64_t stride_floats, void* stream) {
     if (nrows <= 0) return 0;
     int64_t blocks = (nrows + 7) / 8;
-    if (blocks > 148 * 16) blocks = 148 * 16;
+    if (blocks > coala_sm_count() * 16) blocks = coala_sm_count() * 16;
     synth_fill_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(reinterpret_cast<float*>(dst_ptr), seed, row0,
                                                                                    nrows, dim, stride_floats);
     COALA_CUDA(cudaGetLastError());
@@ -127,7 +127,7 @@ extern "C" int coala_synth_check_rows(uint64_t rows_ptr, uint64_t idx_ptr, int64
     COALA_CUDA(cudaMemset(d_bad, 0, 8));
     if (n > 0) {
         int64_t blocks = (n + 7) / 8;
-        if (blocks > 148 * 16) blocks = 148 * 16;
+        if (blocks > coala_sm_count() * 16) blocks = coala_sm_count() * 16;
         synth_check_kernel<<<(unsigned)blocks, 256>>>(reinterpret_cast<const float*>(rows_ptr), reinterpret_cast<const int64_t*>(idx_ptr),
                                                       n, dim, stride_floats, seed, d_bad);
         COALA_CUDA(cudaGetLastError());
@@ -163,9 +163,9 @@ extern "C" int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int i
     COALA_CUDA(cudaEventCreate(&e0));
     COALA_CUDA(cudaEventCreate(&e1));
     const int64_t nvec = bytes / 16;
-    probe_read_kernel<<<148 * 8, 256>>>(reinterpret_cast<const uint4*>(src_ptr), nvec, sink);  // warm-up
+    probe_read_kernel<<<coala_sm_count() * 8, 256>>>(reinterpret_cast<const uint4*>(src_ptr), nvec, sink);  // warm-up
     COALA_CUDA(cudaEventRecord(e0));
-    for (int i = 0; i < iters; i++) probe_read_kernel<<<148 * 8, 256>>>(reinterpret_cast<const uint4*>(src_ptr), nvec, sink);
+    for (int i = 0; i < iters; i++) probe_read_kernel<<<coala_sm_count() * 8, 256>>>(reinterpret_cast<const uint4*>(src_ptr), nvec, sink);
     COALA_CUDA(cudaEventRecord(e1));
     COALA_CUDA(cudaEventSynchronize(e1));
     float ms = 0;
@@ -249,10 +249,10 @@ extern "C" int coala_probe_gather(uint64_t table_ptr, uint64_t idx_ptr, uint64_t
         }
 #undef COALA_PG
     };
-    go(0);  // warm-up (its rows are not reused: timed launches start at it = 1 when there are several)
+    go(0);  // warm-up on list 0; the timed launches read lists 1..iters, so none of them re-reads rows the warm-up left in L2
     COALA_CUDA(cudaDeviceSynchronize());
     COALA_CUDA(cudaEventRecord(e0));
-    for (int i = 0; i < iters; i++) go(iters > 1 ? i : 0);
+    for (int i = 1; i <= iters; i++) go(i);
     COALA_CUDA(cudaEventRecord(e1));
     COALA_CUDA(cudaEventSynchronize(e1));
     COALA_CUDA(cudaGetLastError());
@@ -348,7 +348,7 @@ __global__ void probe_gather_all_kernel(const __grid_constant__ ProbeTables pt, 
 }
 
 // tables[g] = device g's part (peer access between all pairs must be enabled), idx[g] / out[g] = device g's id list
-// (iters * n ids) and output rows; us_per_launch[g] = device g's mean launch time while all G run.  4 KB rows only.
+// ((iters + 1) * n ids: list 0 warms up, lists 1..iters are timed) and output rows; us_per_launch[g] = device g's mean launch time while all G run.  4 KB rows only.
 extern "C" int coala_probe_gather_all(int G, const uint64_t* tables, const uint64_t* idx, const uint64_t* out, int64_t n, int rows_in_flight,
                                       int ctas_per_sm, int iters, double* us_per_launch) {
     if (G < 1 || G > 8) COALA_FAIL("probe_gather_all: 1..8 GPUs");
@@ -374,8 +374,8 @@ extern "C" int coala_probe_gather_all(int G, const uint64_t* tables, const uint6
     for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); go(g, 0); }
     for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); COALA_CUDA(cudaDeviceSynchronize()); }
     for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); COALA_CUDA(cudaEventRecord(e0[g])); }
-    for (int i = 0; i < iters; i++)
-        for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); go(g, iters > 1 ? i : 0); }
+    for (int i = 1; i <= iters; i++)  // list 0 was the warm-up's
+        for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); go(g, i); }
     for (int g = 0; g < G; g++) { COALA_CUDA(cudaSetDevice(g)); COALA_CUDA(cudaEventRecord(e1[g])); }
     for (int g = 0; g < G; g++) {
         COALA_CUDA(cudaSetDevice(g));

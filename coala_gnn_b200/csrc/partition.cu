@@ -197,7 +197,7 @@ int coala_partition_buckets(const int64_t* idx, int64_t n_upper, const int64_t* 
 extern "C" int coala_map_feat_data(uint64_t out_ptr, uint64_t src_ptr, uint64_t map_ptr, int64_t n, int feat_dim, void* stream) {
     if (n <= 0) return 0;
     int64_t blocks = (n + 7) / 8;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > coala_sm_count() * 8) blocks = coala_sm_count() * 8;
     unpermute_rows_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<float*>(out_ptr), reinterpret_cast<const float*>(src_ptr), reinterpret_cast<const int64_t*>(map_ptr), n, feat_dim);
     COALA_CUDA(cudaGetLastError());

@@ -716,7 +716,7 @@ extern "C" int coala_sampler_layer_ptrs(coala_sampler* s, int layer, uint64_t* s
 extern "C" int coala_lookup_edge_ids(uint64_t edge_ids_ptr, uint64_t pos_dev_ptr, int64_t n, uint64_t out_dev_ptr, void* stream) {
     if (n <= 0) return 0;
     int64_t blocks = (n + 255) / 256;
-    if (blocks > 148 * 8) blocks = 148 * 8;
+    if (blocks > coala_sm_count() * 8) blocks = coala_sm_count() * 8;
     edge_id_lookup_kernel<<<(unsigned)blocks, 256, 0, static_cast<cudaStream_t>(stream)>>>(
         reinterpret_cast<const int64_t*>(pos_dev_ptr), nullptr, n, reinterpret_cast<const int64_t*>(edge_ids_ptr),
         reinterpret_cast<int64_t*>(out_dev_ptr));

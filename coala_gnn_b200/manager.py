@@ -65,6 +65,10 @@ class COALA_GNN_Manager(object):
                 self.nccl = NcclExchange(self.COALA_GNN_Cache, comm.device_index, comm.local_gloo_gather, G, comm.local_rank, ms, dim)
         else:
             raise ValueError(f"Unsupported cache backend: {cache_backend}")
+        # Device-side id bounds check: the host table's row count is known here (the reference dereferences any id it is
+        # given).  Without it an id beyond the table - but below 2^40 - would be read from whatever follows the table.
+        if self.is_simulation and getattr(self.sim_buf, "dim", lambda: 0)() == 2:
+            self.COALA_GNN_Cache.set_num_nodes(int(self.sim_buf.shape[0]))
         self._out = [torch.empty((self.max_sample_size, dim), dtype=torch.float32, device=device) for _ in range(2)]
         self._flip = 0
 
@@ -167,8 +171,16 @@ class COALA_GNN_Manager(object):
     def get_cache_data(self, ptr):
         self.COALA_GNN_Cache.get_cache_data(ptr)
 
+    def check_refused_ids(self):
+        """The asynchronous gather zero-fills the row of an id outside the feature table and counts it (the synchronous
+        calls fail on the spot).  Surface that count: raises if any id was refused since the last check."""
+        n = int(self.COALA_GNN_Cache.refused_ids(True))
+        if n:
+            raise RuntimeError("feature gather refused %d node id(s) outside the feature table (rows were zero-filled)" % n)
+
     def print_stats(self):
         self.COALA_GNN_Cache.print_stats()
+        self.check_refused_ids()
 
     def get_aggregate_time(self):
         return self.aggregation_timer

@@ -126,7 +126,8 @@ int coala_cache_read_feature_async(coala_cache* c, uint64_t out_ptr, uint64_t id
                                    uint64_t n_dev_ptr, void* stream);
 /* Node ids are bounds-checked on the device (the reference dereferences whatever it is given): an id >= the host
  * table's row count (known from the distributor's colour table, or set here) or >= 2^40 - 1 (the tag's id field) is
- * refused - its output row is zero-filled and counted.  The synchronous read_feature calls fail when a launch
+ * refused - its output row is zero-filled and counted (set_num_nodes never raises the limit above the colour table's length:
+ * the fill path looks the id's colour up too).  The synchronous read_feature calls fail when a launch
  * refused ids; callers of the async form poll coala_cache_refused_ids. */
 int coala_cache_set_num_nodes(coala_cache* c, int64_t num_nodes);
 int coala_cache_refused_ids(coala_cache* c, uint64_t* count, int reset);
@@ -312,12 +313,12 @@ int coala_probe_read_bandwidth(uint64_t src_ptr, int64_t bytes, int iters, doubl
 int coala_enable_peer_access(int device, int peer);
 
 /* row-gather probe: out[i] = table[idx[i]] with no cache protocol - the practical ceiling of the gather's access pattern on
- * whatever link `table` sits behind (local HBM, a peer's HBM, pinned host).  idx holds iters * n ids (one list per timed
- * launch); rows_in_flight 1|2 per warp; ctas_per_sm CTAs of 256 threads per SM; returns the mean launch time (CUDA events). */
+ * whatever link `table` sits behind (local HBM, a peer's HBM, pinned host).  idx holds (iters + 1) * n ids: list 0 is the
+ * untimed warm-up launch's, lists 1..iters one per timed launch (no timed launch re-reads rows the warm-up left in L2); rows_in_flight 1|2 per warp; ctas_per_sm CTAs of 256 threads per SM; returns the mean launch time (CUDA events). */
 int coala_probe_gather(uint64_t table_ptr, uint64_t idx_ptr, uint64_t out_ptr, int64_t n, int row_bytes, int rows_in_flight,
                        int ctas_per_sm, int iters, double* us_per_launch);
 /* the same with the table hash-partitioned over the G GPUs of this process like the cache (owner id % G, row id / G; 4 KB rows)
- * and all G GPUs gathering at once: tables[g] / idx[g] / out[g] are device g's part, id lists (iters * n) and output rows;
+ * and all G GPUs gathering at once: tables[g] / idx[g] / out[g] are device g's part, id lists ((iters + 1) * n, list 0 = warm-up) and output rows;
  * peer access must be enabled between all pairs; us_per_launch[g] = device g's mean launch time while all run. */
 int coala_probe_gather_all(int G, const uint64_t* tables, const uint64_t* idx, const uint64_t* out, int64_t n, int rows_in_flight,
                            int ctas_per_sm, int iters, double* us_per_launch);

@@ -27,7 +27,7 @@ R, n, iters = args.row_bytes, args.rows, args.iters
 n_rows = int(args.table_gb * (1 << 30)) // R
 rng = np.random.default_rng(0)
 torch.cuda.set_device(0)
-idx = torch.from_numpy(rng.integers(0, n_rows, size=n * iters).astype(np.int64)).cuda()
+idx = torch.from_numpy(rng.integers(0, n_rows, size=n * (iters + 1)).astype(np.int64)).cuda()  # list 0 = warm-up, 1..iters timed
 out = torch.empty(n * R, dtype=torch.uint8, device="cuda:0")
 res = {"config": vars(args), "table_rows": n_rows}
 us = C.c_double()

@@ -31,7 +31,7 @@ for g in range(G):
     torch.cuda.set_device(g)
     tables.append(torch.empty(part_rows * R, dtype=torch.uint8, device="cuda:%d" % g))
     rng = np.random.default_rng(10 + g)
-    idxs.append(torch.from_numpy(rng.integers(0, 1 << 62, size=n * iters).astype(np.int64)).to("cuda:%d" % g))
+    idxs.append(torch.from_numpy(rng.integers(0, 1 << 62, size=n * (iters + 1)).astype(np.int64)).to("cuda:%d" % g))
     outs.append(torch.empty(n * R, dtype=torch.uint8, device="cuda:%d" % g))
 for a in range(G):
     for b in range(G):

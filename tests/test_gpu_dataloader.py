@@ -165,3 +165,31 @@ def test_papers100m_shaped_batch_gat_fanout_full_batch_size(tmp_path, backend):
         assert np.array_equal(rows.view(np.uint32), d["feat"][einp].view(np.uint32))
     h, m, b = loader.COALA_GNN_Manager.COALA_GNN_Cache.stats()
     assert m > 0 and h + m + b > 0
+
+
+def test_ids_outside_the_feature_table_are_surfaced_by_print_stats(tmp_path):
+    """The manager tells the cache how many rows the host table has (sim_buf.shape[0]); the asynchronous gather
+    zero-fills the row of an id beyond it instead of dereferencing it (the reference reads whatever lies there,
+    M/isolated_cache.h:335-475 has no bounds check) and print_stats raises on the count."""
+    import torch
+    from COALA_GNN import Node_Distributor, SSD_INFO, COALA_GNN_DataLoader, MultiLayerNeighborSampler
+    d = _dataset(tmp_path)
+    B, fan, rows = 128, [5, 5], d["n"] - 5000
+    train = torch.from_numpy(synth.train_ids(d["n"], seed=1))
+    nd = Node_Distributor(d["comm"], train, B, *d["files"], parsing_method="baseline")
+    loader = COALA_GNN_DataLoader(SSD_INFO(1, 512, 1024, 0), nd, d["g"], MultiLayerNeighborSampler(fan, seed=5), B, d["dim"], fan, 2,
+                                  "cuda:0", cache_backend="isolated", sim_buf=d["feat_uva"][:rows])  # a table 5000 rows short
+    seen_outside = 0
+    for step, (input_nodes, seeds, blocks, feat) in enumerate(loader):
+        inp = input_nodes.cpu().numpy()
+        inside = inp < rows
+        seen_outside += int((~inside).sum())
+        got = feat.cpu().numpy()
+        assert np.array_equal(got[inside].view(np.uint32), d["feat"][inp[inside]].view(np.uint32))
+        assert not got[~inside].any()
+        if step == 3:
+            break
+    assert seen_outside > 0
+    with pytest.raises(RuntimeError, match="outside the feature table"):
+        loader.print_stats()
+    loader.COALA_GNN_Manager.check_refused_ids()  # the count was reset by the failing check
