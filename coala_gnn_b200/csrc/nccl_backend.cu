@@ -20,6 +20,7 @@
 #include "common.cuh"
 #include "../../include/coala_b200.h"
 #include <dlfcn.h>
+#include <algorithm>
 
 int coala_partition_buckets(const int64_t* idx, int64_t n_upper, const int64_t* n_dev, int64_t* buckets, int64_t* map, int n_gpus,
                             int max_sample, int* block_cnt_scratch, cudaStream_t st);
@@ -37,6 +38,7 @@ struct NcclApi {
     ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
     ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
     ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*CommAbort)(ncclComm_t) = nullptr;
     ncclResult_t (*GroupStart)() = nullptr;
     ncclResult_t (*GroupEnd)() = nullptr;
     ncclResult_t (*Send)(const void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
@@ -62,6 +64,7 @@ int load_nccl() {
     COALA_SYM(GetUniqueId, "ncclGetUniqueId")
     COALA_SYM(CommInitRank, "ncclCommInitRank")
     COALA_SYM(CommDestroy, "ncclCommDestroy")
+    COALA_SYM(CommAbort, "ncclCommAbort")
     COALA_SYM(GroupStart, "ncclGroupStart")
     COALA_SYM(GroupEnd, "ncclGroupEnd")
     COALA_SYM(Send, "ncclSend")
@@ -176,7 +179,7 @@ extern "C" coala_nccl* coala_nccl_create(coala_cache* shard, int device, const v
     x->shard = shard; x->device = device; x->G = n_ranks; x->rank = rank; x->dim = feat_dim; x->max_sample = (int)max_sample;
     x->stride = 1 + max_sample;
     // id % G spreads a batch evenly over the owners: a rank serves about as many rows as it asks for (<= max_sample);
-    // twice that is allowed for, beyond it the call fails instead of overrunning
+    // twice that is allocated up front, a batch that needs more grows the buffers (up to G x max_sample, the true bound)
     x->served_cap = 2 * max_sample;
     const size_t bucket_bytes = (size_t)n_ranks * x->stride * 8;
 #define COALA_ALLOC(ptr, bytes)                                                                                 \
@@ -244,14 +247,39 @@ extern "C" int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t 
         ask.v[g + 1] = ask.v[g] + x->h_counts[g];
         serve.v[g + 1] = serve.v[g] + x->h_counts[G + g];
     }
-    if (serve.v[G] > x->served_cap) COALA_FAIL("nccl fetch: this rank was asked for more rows than its serve buffer holds (2 x max_sample)");
+    // Between here and the row exchange a plain error return would leave every peer blocked for ever in its ncclRecv (they
+    // have this rank's id buckets already and expect its rows).  So nothing here fails locally: a batch that concentrates
+    // on this owner - legal, the worst case is G x max_sample rows when the ids are skewed so that id % G favours it -
+    // grows the serve buffers, and what cannot be recovered (out of memory, a failed cache launch) aborts the communicator,
+    // which fails the peers' pending operations instead of hanging them.
+    auto abort_domain = [&](const std::string& why) {
+        if (x->comm) { g_nccl.CommAbort(x->comm); x->comm = nullptr; }
+        coala_set_error("nccl fetch: " + why + "; the domain's communicator was aborted (every rank's exchange fails)");
+        return -1;
+    };
+    if (serve.v[G] > x->served_cap) {
+        int64_t cap = std::max<int64_t>(serve.v[G], 2 * x->served_cap);
+        cap = std::min<int64_t>(cap, (int64_t)G * x->max_sample);
+        float* ns = nullptr;
+        int64_t* np = nullptr;
+        // the stream was synchronised for the counts: nothing enqueued earlier still uses the old buffers
+        cudaFree(x->served); cudaFree(x->packed);
+        x->served = nullptr; x->packed = nullptr; x->served_cap = 0;
+        if (cudaMalloc(&ns, (size_t)cap * x->dim * 4) != cudaSuccess || cudaMalloc(&np, (size_t)cap * 8) != cudaSuccess) {
+            (void)cudaGetLastError();
+            cudaFree(ns);
+            return abort_domain("out of memory growing the serve buffers to " + std::to_string(cap) + " rows");
+        }
+        x->served = ns; x->packed = np; x->served_cap = cap;
+    }
     // 4. owner side: one list, one launch of the gather kernel against this rank's shard
     if (serve.v[G] > 0) {
         int64_t blocks = (serve.v[G] + 255) / 256;
-        if (blocks > 148 * 4) blocks = 148 * 4;
+        if (blocks > coala_sm_count() * 4) blocks = coala_sm_count() * 4;
         nx_pack_ids_kernel<<<(unsigned)blocks, 256, 0, st>>>(x->recv_b, G, stride, serve, x->packed);
-        COALA_CUDA(cudaGetLastError());
-        if (coala_cache_read_feature_async(x->shard, (uint64_t)x->served, (uint64_t)x->packed, serve.v[G], 0, st)) return -1;
+        if (cudaError_t le = cudaGetLastError(); le != cudaSuccess) return abort_domain(std::string("pack launch failed: ") + cudaGetErrorString(le));
+        if (coala_cache_read_feature_async(x->shard, (uint64_t)x->served, (uint64_t)x->packed, serve.v[G], 0, st))
+            return abort_domain(std::string("owner-side cache read failed (") + coala_last_error() + ")");
     }
     // 5. rows: one grouped exchange, exact counts
     const size_t rowf = (size_t)x->dim;
@@ -271,7 +299,7 @@ extern "C" int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t 
     // 6. bucket order -> request order
     if (ask.v[G] > 0) {
         int64_t blocks = (ask.v[G] + 7) / 8;
-        if (blocks > 148 * 8) blocks = 148 * 8;
+        if (blocks > coala_sm_count() * 8) blocks = coala_sm_count() * 8;
         nx_unpermute_kernel<<<(unsigned)blocks, 256, 0, st>>>(reinterpret_cast<float*>(out_ptr), x->rows_in, x->map, G, x->max_sample, ask, x->dim,
                                                              x->dim);
         COALA_CUDA(cudaGetLastError());
