@@ -226,18 +226,20 @@ extern "C" int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t 
     if (coala_partition_buckets(reinterpret_cast<const int64_t*>(idx_ptr), n_upper, reinterpret_cast<const int64_t*>(n_dev_ptr), x->send_b, x->map, G,
                                 x->max_sample, x->block_cnt, st))
         return -1;
-    // 2. ids: one grouped exchange of fixed-size buckets (the header carries the count)
+    // 2. bucket sizes first: one grouped exchange of the G header words (8 bytes per peer).  The reference pads every id
+    // bucket to max_sample words (S/COALA_GNN_Manager.py:161-165: 2.4 MB per rank per batch at G = 8); knowing the sizes
+    // up front, step 4 ships exact-length id lists and the comparison with the P2P backend is about NCCL, not padding.
     if (G > 1) {
         COALA_NCCL(g_nccl.GroupStart());
         for (int g = 0; g < G; g++) {
             if (g == me) continue;
-            COALA_NCCL(g_nccl.Send(x->send_b + g * stride, (size_t)stride, NCCL_INT64, g, x->comm, st));
-            COALA_NCCL(g_nccl.Recv(x->recv_b + g * stride, (size_t)stride, NCCL_INT64, g, x->comm, st));
+            COALA_NCCL(g_nccl.Send(x->send_b + g * stride, 1, NCCL_INT64, g, x->comm, st));
+            COALA_NCCL(g_nccl.Recv(x->recv_b + g * stride, 1, NCCL_INT64, g, x->comm, st));
         }
         COALA_NCCL(g_nccl.GroupEnd());
     }
     COALA_CUDA(cudaMemcpyAsync(x->recv_b + me * stride, x->send_b + me * stride, (size_t)stride * 8, cudaMemcpyDeviceToDevice, st));
-    // 3. the counts are the one thing the host has to know (element counts of the row exchange)
+    // 3. the counts are the one thing the host has to know (element counts of both exchanges that follow)
     nx_counts_kernel<<<1, 32, 0, st>>>(x->send_b, x->recv_b, G, stride, x->d_counts);
     COALA_CUDA(cudaMemcpyAsync(x->h_counts, x->d_counts, 2 * G * 8, cudaMemcpyDeviceToHost, st));
     COALA_CUDA(cudaStreamSynchronize(st));
@@ -248,7 +250,7 @@ extern "C" int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t 
         serve.v[g + 1] = serve.v[g] + x->h_counts[G + g];
     }
     // Between here and the row exchange a plain error return would leave every peer blocked for ever in its ncclRecv (they
-    // have this rank's id buckets already and expect its rows).  So nothing here fails locally: a batch that concentrates
+    // know this rank's bucket sizes already and post the matching receives of ids and rows).  So nothing here fails locally: a batch that concentrates
     // on this owner - legal, the worst case is G x max_sample rows when the ids are skewed so that id % G favours it -
     // grows the serve buffers, and what cannot be recovered (out of memory, a failed cache launch) aborts the communicator,
     // which fails the peers' pending operations instead of hanging them.
@@ -272,7 +274,18 @@ extern "C" int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t 
         }
         x->served = ns; x->packed = np; x->served_cap = cap;
     }
-    // 4. owner side: one list, one launch of the gather kernel against this rank's shard
+    // 4. ids: one grouped exchange, exact lengths (bucket g's ids follow its header word)
+    if (G > 1) {
+        COALA_NCCL(g_nccl.GroupStart());
+        for (int g = 0; g < G; g++) {
+            if (g == me) continue;
+            const int64_t na = ask.v[g + 1] - ask.v[g], nsv = serve.v[g + 1] - serve.v[g];
+            if (na > 0) COALA_NCCL(g_nccl.Send(x->send_b + g * stride + 1, (size_t)na, NCCL_INT64, g, x->comm, st));
+            if (nsv > 0) COALA_NCCL(g_nccl.Recv(x->recv_b + g * stride + 1, (size_t)nsv, NCCL_INT64, g, x->comm, st));
+        }
+        COALA_NCCL(g_nccl.GroupEnd());
+    }
+    // 5. owner side: one list, one launch of the gather kernel against this rank's shard
     if (serve.v[G] > 0) {
         int64_t blocks = (serve.v[G] + 255) / 256;
         if (blocks > coala_sm_count() * 4) blocks = coala_sm_count() * 4;
@@ -281,7 +294,7 @@ extern "C" int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t 
         if (coala_cache_read_feature_async(x->shard, (uint64_t)x->served, (uint64_t)x->packed, serve.v[G], 0, st))
             return abort_domain(std::string("owner-side cache read failed (") + coala_last_error() + ")");
     }
-    // 5. rows: one grouped exchange, exact counts
+    // 6. rows: one grouped exchange, exact counts
     const size_t rowf = (size_t)x->dim;
     if (G > 1) {
         COALA_NCCL(g_nccl.GroupStart());
@@ -296,7 +309,7 @@ extern "C" int coala_nccl_fetch_async(coala_nccl* x, uint64_t out_ptr, uint64_t 
     const int64_t n_self = ask.v[me + 1] - ask.v[me];
     if (n_self > 0)
         COALA_CUDA(cudaMemcpyAsync(x->rows_in + ask.v[me] * rowf, x->served + serve.v[me] * rowf, (size_t)n_self * rowf * 4, cudaMemcpyDeviceToDevice, st));
-    // 6. bucket order -> request order
+    // 7. bucket order -> request order
     if (ask.v[G] > 0) {
         int64_t blocks = (ask.v[G] + 7) / 8;
         if (blocks > coala_sm_count() * 8) blocks = coala_sm_count() * 8;
